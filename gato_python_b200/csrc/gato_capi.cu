@@ -1,0 +1,213 @@
+// gato_capi.cu -- host side of the C ABI declared in include/gato_b200.h.
+//
+// Replaces the reference's host driver (main_call / gato_linsys, gpu_library.cu:25-231): the
+// sparsity pattern is analysed once into scatter maps (a "plan"), device buffers are persistent,
+// and a solve is H2D -> ONE fused kernel -> D2H with no allocation and a single host sync.
+// There is no CPU fallback: without a CUDA device every entry point fails with GATO_ENODEVICE.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/gato_b200.h"
+#include "gato_kernels.cuh"
+
+#ifndef GATO_EXTRA_S
+#define GATO_EXTRA_S 0
+#define GATO_EXTRA_C 0
+#endif
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define GATO_CUDA(expr)                                                                   \
+    do {                                                                                  \
+        cudaError_t e_ = (expr);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver      \
+                            ? GATO_ENODEVICE : (int)e_,                                   \
+                        "%s: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= bytes) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+
+struct PinBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= bytes) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMallocHost(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+};
+
+}  // namespace
+
+struct gato_plan {
+    int S, C, K, nnzG, nnzC, device, max_batch;
+    int n_z, n_l, g_dense, c_dense;
+    int cl_override = 0;
+    int sm_count = 0;
+    int smem_optin = 0;
+    // device: pattern maps
+    int *d_gmap = nullptr, *d_cmap = nullptr, *d_gstart = nullptr, *d_cstart = nullptr;
+    // device: staged inputs / outputs for the host-buffer entry points
+    DevBuf dG, dC, dg, dc, dl, dlo, ddz, dit, dbg;
+    PinBuf hin, hout;   // pinned staging for the single-solve path
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+// ------------------------------------------------------------------------------------------------
+// kernel dispatch
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct LaunchCfg { int cl, kpc, maxw; size_t smem; };
+
+template <int S, int C>
+int pick_cfg(const gato_plan* pl, LaunchCfg* out) {
+    using L = gato::Layout<S, C>;
+    const int K = pl->K;
+    auto fits = [&](int cl, int kpc) {
+        return kpc <= 32 && (size_t)L::cta_floats(kpc, cl) * 4 <= (size_t)pl->smem_optin;
+    };
+    int cl = pl->cl_override;
+    if (cl <= 0) {
+        // default: the fewest CTAs whose warps (one per knot) still fit one CTA each -- fewer
+        // CTAs means fewer DSMEM hops per cluster barrier
+        for (cl = 1; cl <= 16; cl *= 2)
+            if (fits(cl, (K + cl - 1) / cl)) break;
+    }
+    if (cl < 1 || cl > 16) return fail(GATO_EUNSUPPORTED, "K=%d does not fit one 16-CTA cluster", K);
+    const int kpc = (K + cl - 1) / cl;
+    if (!fits(cl, kpc))
+        return fail(GATO_EUNSUPPORTED, "cluster of %d CTAs x %d knots does not fit (K=%d, smem %d B)",
+                    cl, kpc, K, pl->smem_optin);
+    out->cl = cl;
+    out->kpc = kpc;
+    out->maxw = kpc <= 16 ? 16 : 32;
+    out->smem = (size_t)L::cta_floats(kpc, cl) * 4;
+    return GATO_OK;
+}
+
+template <int S, int C, int MAXW>
+int launch_t(const LaunchCfg& cfg, const gato::SolveParams& p, cudaStream_t st) {
+    auto kern = gato::gato_fused_solve<S, C, MAXW>;
+    GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
+    if (cfg.cl > 8)
+        GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)(p.nsys * cfg.cl), 1, 1);
+    lc.blockDim = dim3((unsigned)(cfg.kpc * 32), 1, 1);
+    lc.dynamicSmemBytes = cfg.smem;
+    lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)cfg.cl;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    lc.attrs = at;
+    lc.numAttrs = 1;
+    GATO_CUDA(cudaLaunchKernelEx(&lc, kern, p));
+    return GATO_OK;
+}
+
+template <int S, int C>
+int launch_sc(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+    LaunchCfg cfg;
+    int rc = pick_cfg<S, C>(pl, &cfg);
+    if (rc) return rc;
+    return cfg.maxw == 16 ? launch_t<S, C, 16>(cfg, p, st) : launch_t<S, C, 32>(cfg, p, st);
+}
+
+template <int S, int C>
+int unpack_sc(const gato_plan* pl, const float* dG, const float* dC, float* Gd, float* Cd, float rho,
+              cudaStream_t st) {
+    const int warps_per_block = 4;
+    const int blocks = (pl->K + warps_per_block - 1) / warps_per_block;
+    gato::gato_unpack_kernel<S, C><<<blocks, warps_per_block * 32, 0, st>>>(
+        pl->d_gmap, pl->d_cmap, pl->d_gstart, pl->d_cstart, dG, dC, Gd, Cd, pl->K, rho);
+    GATO_CUDA(cudaGetLastError());
+    return GATO_OK;
+}
+
+#define GATO_FOR_SIZES(X) X(2, 1) X(14, 7)
+
+bool size_supported(int S, int C) {
+#define X(s, c) if (S == s && C == c) return true;
+    GATO_FOR_SIZES(X)
+#undef X
+#if GATO_EXTRA_S > 0
+    if (S == GATO_EXTRA_S && C == GATO_EXTRA_C) return true;
+#endif
+    return false;
+}
+
+int launch_solve(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+#define X(s, c) if (pl->S == s && pl->C == c) return launch_sc<s, c>(pl, p, st);
+    GATO_FOR_SIZES(X)
+#undef X
+#if GATO_EXTRA_S > 0
+    if (pl->S == GATO_EXTRA_S && pl->C == GATO_EXTRA_C)
+        return launch_sc<GATO_EXTRA_S, GATO_EXTRA_C>(pl, p, st);
+#endif
+    return fail(GATO_EUNSUPPORTED, "no kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+int launch_unpack(const gato_plan* pl, const float* dG, const float* dC, float* Gd, float* Cd,
+                  float rho, cudaStream_t st) {
+#define X(s, c) if (pl->S == s && pl->C == c) return unpack_sc<s, c>(pl, dG, dC, Gd, Cd, rho, st);
+    GATO_FOR_SIZES(X)
+#undef X
+#if GATO_EXTRA_S > 0
+    if (pl->S == GATO_EXTRA_S && pl->C == GATO_EXTRA_C)
+        return unpack_sc<GATO_EXTRA_S, GATO_EXTRA_C>(pl, dG, dC, Gd, Cd, rho, st);
+#endif
+    return fail(GATO_EUNSUPPORTED, "no kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+int cfg_for(const gato_plan* pl, LaunchCfg* cfg) {
+#define X(s, c) if (pl->S == s && pl->C == c) return pick_cfg<s, c>(pl, cfg);
+    GATO_FOR_SIZES(X)
+#undef X
+#if GATO_EXTRA_S > 0
+    if (pl->S == GATO_EXTRA_S && pl->C == GATO_EXTRA_C)
+        return pick_cfg<GATO_EXTRA_S, GATO_EXTRA_C>(pl, cfg);
+#endif
+    return fail(GATO_EUNSUPPORTED, "no kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+}  // namespace
+
+#include "gato_capi_entry.inc"

@@ -1,0 +1,186 @@
+// gpu_library.cu -- pybind11 drop-in for the reference module of the same name.
+//
+// Keeps the surface of /root/reference/gpu_library.cu:85-87, 236-239:
+//   gpu_library.linsys_solve(G_row, G_col, G_val, C_row, C_col, C_val, g_val, c_val, input_lambda,
+//                            testiters, exit_tol, max_iters, warm_start, rho) -> (lambda, dz)
+// with the compile-time knobs STATE_SIZE / CONTROL_SIZE / KNOT_POINTS (CMakeLists.txt:18).
+// Everything numerical happens behind the C ABI (include/gato_b200.h).  Differences from the
+// reference, all at the boundary (SURVEY.md 8b "EXT"): argument sizes are validated (ValueError
+// instead of undefined behaviour), CUDA failures raise RuntimeError instead of exit(), the
+// iteration count is also returned by linsys_solve_info(), the plan (pattern analysis + device
+// workspace) persists between calls with the same sparsity pattern.
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/gato_b200.h"
+
+#if !defined(STATE_SIZE) || !defined(CONTROL_SIZE) || !defined(KNOT_POINTS)
+#error "build with -DSTATE_SIZE=.. -DCONTROL_SIZE=.. -DKNOT_POINTS=.."
+#endif
+
+namespace py = pybind11;
+
+namespace {
+
+constexpr int kS = STATE_SIZE, kC = CONTROL_SIZE, kK = KNOT_POINTS;
+constexpr int kNz = (kS + kC) * kK - kC, kNl = kS * kK;
+
+struct Cache {
+    gato_plan* plan = nullptr;
+    std::vector<int> G_row, G_col, C_row, C_col;
+    int last_iters = -1;
+    float first_ms = 0.f, avg_ms = 0.f;
+    bool true_warm = false;
+    ~Cache() { /* the CUDA context may already be gone at interpreter exit: leak the plan */ }
+} g_cache;
+
+void check(int rc) {
+    if (rc == GATO_OK) return;
+    const std::string msg = gato_last_error();
+    if (rc == GATO_EINVAL || rc == GATO_EPATTERN) throw py::value_error(msg);
+    throw std::runtime_error("gato_b200: " + msg + " (code " + std::to_string(rc) + ")");
+}
+
+bool quiet() {
+    const char* q = std::getenv("GATO_B200_QUIET");
+    return q && q[0] && q[0] != '0';
+}
+
+gato_plan* plan_for(const std::vector<int>& G_row, const std::vector<int>& G_col,
+                    const std::vector<int>& C_row, const std::vector<int>& C_col) {
+    Cache& c = g_cache;
+    if (c.plan && c.G_row == G_row && c.G_col == G_col && c.C_row == C_row && c.C_col == C_col)
+        return c.plan;
+    if (c.plan) { gato_plan_destroy(c.plan); c.plan = nullptr; }
+    int dev = 0;
+    if (const char* d = std::getenv("GATO_B200_DEVICE")) dev = std::atoi(d);
+    check(gato_plan_create(kS, kC, kK, G_row.data(), G_col.data(), (int)G_col.size(), C_row.data(),
+                           C_col.data(), (int)C_col.size(), dev, 1, &c.plan));
+    c.G_row = G_row; c.G_col = G_col; c.C_row = C_row; c.C_col = C_col;
+    return c.plan;
+}
+
+void check_sizes(size_t G_row, size_t G_col, size_t G_val, size_t C_row, size_t C_col, size_t C_val,
+                 size_t g, size_t c, size_t lam) {
+    auto bad = [](const char* name, size_t got, size_t want) {
+        throw py::value_error(std::string(name) + " has " + std::to_string(got) + " entries, expected " +
+                              std::to_string(want) + " for STATE_SIZE=" + std::to_string(kS) +
+                              " CONTROL_SIZE=" + std::to_string(kC) + " KNOT_POINTS=" + std::to_string(kK));
+    };
+    if (G_row != (size_t)kNz + 1) bad("G_row", G_row, kNz + 1);
+    if (C_row != (size_t)kNl + 1) bad("C_row", C_row, kNl + 1);
+    if (G_col != G_val) bad("G_val", G_val, G_col);
+    if (C_col != C_val) bad("C_val", C_val, C_col);
+    if (g != (size_t)kNz) bad("g_val", g, kNz);
+    if (c != (size_t)kNl) bad("c_val", c, kNl);
+    if (lam < (size_t)kNl) bad("input_lambda", lam, kNl);
+}
+
+py::tuple linsys_solve(std::vector<int> G_row, std::vector<int> G_col, std::vector<float> G_val,
+                       std::vector<int> C_row, std::vector<int> C_col, std::vector<float> C_val,
+                       std::vector<float> g_val, std::vector<float> c_val,
+                       std::vector<float> input_lambda, int testiters, float exit_tol, int max_iters,
+                       bool warm_start, float rho) {
+    check_sizes(G_row.size(), G_col.size(), G_val.size(), C_row.size(), C_col.size(), C_val.size(),
+                g_val.size(), c_val.size(), input_lambda.size());
+    if (testiters < 1) throw py::value_error("testiters must be >= 1");
+    gato_plan* plan = plan_for(G_row, G_col, C_row, C_col);
+    std::vector<float> lambda(input_lambda.begin(), input_lambda.begin() + kNl), lam_out(kNl), dz(kNz);
+    const int warm = !warm_start ? GATO_WARM_OFF
+                                 : (g_cache.true_warm ? GATO_WARM_TRUE : GATO_WARM_REFERENCE);
+    double total = 0.0;
+    int first_iters = 0;
+    float first_ms = 0.f;
+    {
+        py::gil_scoped_release nogil;
+        for (int i = 0; i < testiters; ++i) {   // the reference repeats the whole solve (gpu_library.cu:169-192)
+            int iters = 0;
+            float ms = 0.f;
+            int rc = gato_solve(plan, G_val.data(), C_val.data(), g_val.data(), c_val.data(), lambda.data(),
+                                lam_out.data(), dz.data(), exit_tol, max_iters, warm, rho, &iters, &ms);
+            if (rc) { py::gil_scoped_acquire gil; check(rc); }
+            total += ms;
+            if (i == 0) { first_iters = iters; first_ms = ms; }
+            g_cache.last_iters = iters;
+        }
+    }
+    g_cache.first_ms = first_ms;
+    g_cache.avg_ms = (float)(total / testiters);
+    if (!quiet()) {   // same two summary lines as gpu_library.cu:190,198 (log-scraping callers)
+        std::printf("first run PCG terminated in %d iterations, time:  %f\n", first_iters, first_ms);
+        std::printf("avg time: %f\n", g_cache.avg_ms);
+        std::fflush(stdout);
+    }
+    py::list l, d;
+    for (int i = 0; i < kNl; ++i) l.append(lam_out[i]);
+    for (int i = 0; i < kNz; ++i) d.append(dz[i]);
+    return py::make_tuple(l, d);
+}
+
+py::dict linsys_solve_info() {
+    py::dict d;
+    d["iters"] = g_cache.last_iters;
+    d["first_ms"] = g_cache.first_ms;
+    d["avg_ms"] = g_cache.avg_ms;
+    int cl = 0, kpc = 0;
+    if (g_cache.plan && gato_plan_get_cluster(g_cache.plan, &cl, &kpc) == GATO_OK) {
+        d["cluster_ctas"] = cl;
+        d["knots_per_cta"] = kpc;
+    }
+    return d;
+}
+
+using farr = py::array_t<float, py::array::c_style | py::array::forcecast>;
+using iarr = py::array_t<int, py::array::c_style | py::array::forcecast>;
+
+// EXT: batch of systems over one pattern, NumPy in / NumPy out, no list boxing.
+py::tuple linsys_solve_batched(iarr G_row, iarr G_col, farr G_val, iarr C_row, iarr C_col, farr C_val,
+                               farr g_val, farr c_val, float exit_tol, int max_iters, float rho) {
+    if (G_val.ndim() != 2 || C_val.ndim() != 2 || g_val.ndim() != 2 || c_val.ndim() != 2)
+        throw py::value_error("G_val, C_val, g_val, c_val must be [nsys, n] arrays");
+    const int nsys = (int)g_val.shape(0);
+    check_sizes(G_row.size(), G_col.size(), G_val.shape(1), C_row.size(), C_col.size(), C_val.shape(1),
+                g_val.shape(1), c_val.shape(1), kNl);
+    auto rows_ok = [&](const farr& a) { return a.shape(0) == nsys || a.shape(0) == 1; };
+    if (!rows_ok(G_val) || !rows_ok(C_val) || !rows_ok(c_val))
+        throw py::value_error("leading dimensions must be nsys or 1 (shared)");
+    std::vector<int> gr(G_row.data(), G_row.data() + G_row.size()), gc(G_col.data(), G_col.data() + G_col.size());
+    std::vector<int> cr(C_row.data(), C_row.data() + C_row.size()), cc(C_col.data(), C_col.data() + C_col.size());
+    gato_plan* plan = plan_for(gr, gc, cr, cc);
+    py::array_t<float> lam({nsys, kNl}), dz({nsys, kNz});
+    py::array_t<int> iters(nsys);
+    auto ld = [&](const farr& a) -> long long { return a.shape(0) == 1 && nsys > 1 ? 0 : (long long)a.shape(1); };
+    float ms = 0.f;
+    int rc;
+    {
+        py::gil_scoped_release nogil;
+        rc = gato_solve_batched(plan, nsys, G_val.data(), ld(G_val), C_val.data(), ld(C_val), g_val.data(),
+                                ld(g_val), c_val.data(), ld(c_val), nullptr, 0, lam.mutable_data(),
+                                dz.mutable_data(), iters.mutable_data(), exit_tol, max_iters, GATO_WARM_OFF,
+                                rho, &ms);
+    }
+    check(rc);
+    g_cache.avg_ms = g_cache.first_ms = ms;
+    return py::make_tuple(lam, dz, iters);
+}
+
+}  // namespace
+
+PYBIND11_MODULE(gpu_library, m) {
+    m.doc() = "B200-native GATO KKT linear-system solve (drop-in for the reference gpu_library)";
+    m.attr("STATE_SIZE") = kS;
+    m.attr("CONTROL_SIZE") = kC;
+    m.attr("KNOT_POINTS") = kK;
+    m.def("linsys_solve", &linsys_solve);   // positional, like the reference (no py::arg names)
+    m.def("linsys_solve_info", &linsys_solve_info);
+    m.def("linsys_solve_batched", &linsys_solve_batched);
+    m.def("set_true_warm_start", [](bool on) { g_cache.true_warm = on; });
+    m.def("set_cluster", [](int cl) { if (g_cache.plan) check(gato_plan_set_cluster(g_cache.plan, cl)); });
+}

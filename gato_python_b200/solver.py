@@ -1,0 +1,251 @@
+"""ctypes binding of the C ABI (include/gato_b200.h) and a host-side mirror of the reference's
+operator interface `gpu_library.linsys_solve` (/root/reference/gpu_library.cu:85-87, 236-239).
+
+There is NO CPU fallback here: if `libgato_b200.so` is missing the import of the library fails,
+and if no CUDA device is present every solve raises `GatoError`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgato_b200.so")
+
+WARM_OFF, WARM_REFERENCE, WARM_TRUE = 0, 1, 2
+
+#: every symbol include/gato_b200.h declares
+SYMBOLS = [
+    "gato_supported_sizes", "gato_last_error", "gato_device_count", "gato_plan_create",
+    "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_solve",
+    "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
+]
+
+
+class GatoError(RuntimeError):
+    pass
+
+
+_lib = None
+_fp = C.POINTER(C.c_float)
+_ip = C.POINTER(C.c_int)
+_ll = C.c_longlong
+
+
+def lib():
+    """Load the native library (fails loudly when it has not been built)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise GatoError(f"{LIB_PATH} not built: run `python -m gato_python_b200.build` "
+                        "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    L.gato_last_error.restype = C.c_char_p
+    L.gato_supported_sizes.argtypes = [_ip, C.c_int]
+    L.gato_plan_create.argtypes = [C.c_int] * 3 + [_ip, _ip, C.c_int, _ip, _ip, C.c_int, C.c_int, C.c_int,
+                                                  C.POINTER(C.c_void_p)]
+    L.gato_plan_destroy.argtypes = [C.c_void_p]
+    L.gato_plan_destroy.restype = None
+    L.gato_plan_set_cluster.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_get_cluster.argtypes = [C.c_void_p, _ip, _ip]
+    L.gato_solve.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_int,
+                             C.c_float, _ip, _fp]
+    L.gato_solve_batched.argtypes = [C.c_void_p, C.c_int, _fp, _ll, _fp, _ll, _fp, _ll, _fp, _ll, _fp, _ll,
+                                     _fp, _fp, _ip, C.c_float, C.c_int, C.c_int, C.c_float, _fp]
+    L.gato_solve_batched_device.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p, _ll] * 5 + \
+        [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_float, C.c_void_p]
+    L.gato_unpack.argtypes = [C.c_void_p, _fp, _fp, C.c_float, _fp, _fp]
+    L.gato_solve_debug.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_float,
+                                   _ip, _fp, _fp, _fp, _fp]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        msg = lib().gato_last_error().decode()
+        if rc in (-1, -2):
+            raise ValueError(msg)
+        raise GatoError(f"{msg} (code {rc})")
+
+
+def _f(a):
+    return a.ctypes.data_as(_fp)
+
+
+def _i(a):
+    return a.ctypes.data_as(_ip)
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if shape is not None and a.shape != shape:
+        raise ValueError(f"expected shape {shape}, got {a.shape}")
+    return a
+
+
+def supported_sizes():
+    buf = (C.c_int * 32)()
+    n = lib().gato_supported_sizes(buf, 16)
+    return [(buf[2 * i], buf[2 * i + 1]) for i in range(min(n, 16))]
+
+
+def device_count():
+    return lib().gato_device_count()
+
+
+class Plan:
+    """Sparsity pattern + persistent device workspace for one (S, C, K) on one GPU."""
+
+    def __init__(self, S, C_, K, G_row, G_col, C_row, C_col, device=0, max_batch=1):
+        self.S, self.C, self.K = int(S), int(C_), int(K)
+        self.n_z = (self.S + self.C) * self.K - self.C
+        self.n_l = self.S * self.K
+        self.g_dense = (self.S ** 2 + self.C ** 2) * self.K - self.C ** 2
+        self.c_dense = (self.S ** 2 + self.S * self.C) * (self.K - 1)
+        self.device = int(device)
+        gr = np.ascontiguousarray(G_row, np.int32)
+        gc = np.ascontiguousarray(G_col, np.int32)
+        cr = np.ascontiguousarray(C_row, np.int32)
+        cc = np.ascontiguousarray(C_col, np.int32)
+        if gr.size != self.n_z + 1 or cr.size != self.n_l + 1:
+            raise ValueError(f"G_row/C_row must have {self.n_z + 1}/{self.n_l + 1} entries "
+                             f"(got {gr.size}/{cr.size})")
+        self.nnzG, self.nnzC = int(gc.size), int(cc.size)
+        h = C.c_void_p()
+        _check(lib().gato_plan_create(self.S, self.C, self.K, _i(gr), _i(gc), self.nnzG, _i(cr), _i(cc),
+                                      self.nnzC, self.device, int(max_batch), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().gato_plan_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def set_cluster(self, cluster_ctas):
+        _check(lib().gato_plan_set_cluster(self._h, int(cluster_ctas)))
+
+    def cluster(self):
+        a, b = C.c_int(), C.c_int()
+        _check(lib().gato_plan_get_cluster(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    # -- single system, host buffers -------------------------------------------------------------
+    def solve(self, G_val, C_val, g, c, lambda_in=None, exit_tol=1e-6, max_iters=500, warm_start=WARM_OFF,
+              rho=0.0):
+        """-> (lambda [S*K], dz [(S+C)K-C], info{iters, device_ms})"""
+        G_val = _f32(G_val, (self.nnzG,)); C_val = _f32(C_val, (self.nnzC,))
+        g = _f32(g, (self.n_z,)); c = _f32(c, (self.n_l,))
+        lam_in = _f32(lambda_in, (self.n_l,)) if lambda_in is not None else None
+        lam = np.empty(self.n_l, np.float32)
+        dz = np.empty(self.n_z, np.float32)
+        it, ms = C.c_int(), C.c_float()
+        _check(lib().gato_solve(self._h, _f(G_val), _f(C_val), _f(g), _f(c),
+                                _f(lam_in) if lam_in is not None else None, _f(lam), _f(dz),
+                                exit_tol, int(max_iters), int(warm_start), rho, C.byref(it), C.byref(ms)))
+        return lam, dz, dict(iters=it.value, device_ms=ms.value)
+
+    # -- batch, host buffers ---------------------------------------------------------------------
+    def solve_batched(self, G_val, C_val, g, c, lambda_in=None, exit_tol=1e-6, max_iters=500,
+                      warm_start=WARM_OFF, rho=0.0):
+        """Arrays are [nsys, n] or [n] (shared by all systems).  -> (lambda, dz, iters, device_ms)"""
+        g = np.ascontiguousarray(g, np.float32)
+        if g.ndim != 2 or g.shape[1] != self.n_z:
+            raise ValueError(f"g must be [nsys, {self.n_z}]")
+        nsys = g.shape[0]
+
+        def prep(a, n):
+            a = np.ascontiguousarray(a, np.float32)
+            if a.ndim == 1:
+                a = a[None]
+            if a.shape[1] != n or a.shape[0] not in (1, nsys):
+                raise ValueError(f"expected [{nsys} or 1, {n}], got {a.shape}")
+            return a, (0 if (a.shape[0] == 1 and nsys > 1) else n)
+
+        G_val, ldG = prep(G_val, self.nnzG)
+        C_val, ldC = prep(C_val, self.nnzC)
+        c, ldc = prep(c, self.n_l)
+        lam_in, ldl = (prep(lambda_in, self.n_l) if lambda_in is not None else (None, 0))
+        lam = np.empty((nsys, self.n_l), np.float32)
+        dz = np.empty((nsys, self.n_z), np.float32)
+        iters = np.empty(nsys, np.int32)
+        ms = C.c_float()
+        _check(lib().gato_solve_batched(self._h, nsys, _f(G_val), ldG, _f(C_val), ldC, _f(g), self.n_z,
+                                        _f(c), ldc, _f(lam_in) if lam_in is not None else None, ldl,
+                                        _f(lam), _f(dz), _i(iters), exit_tol, int(max_iters),
+                                        int(warm_start), rho, C.byref(ms)))
+        return lam, dz, iters, ms.value
+
+    # -- batch, device pointers (ints), asynchronous ----------------------------------------------
+    def solve_batched_device(self, nsys, dG, ldG, dC, ldC, dg, ldg, dc, ldc, dlam_out, ddz_out, diters_out,
+                             dlam_in=0, ldl=0, exit_tol=1e-6, max_iters=500, warm_start=WARM_OFF, rho=0.0,
+                             stream=0):
+        _check(lib().gato_solve_batched_device(self._h, int(nsys), dG, ldG, dC, ldC, dg, ldg, dc, ldc,
+                                               dlam_in or None, ldl, dlam_out, ddz_out, diters_out, exit_tol,
+                                               int(max_iters), int(warm_start), rho, stream or None))
+
+    # -- parity hooks ----------------------------------------------------------------------------
+    def unpack(self, G_val, C_val, rho):
+        G_val = _f32(G_val, (self.nnzG,)); C_val = _f32(C_val, (self.nnzC,))
+        Gd = np.empty(self.g_dense, np.float32)
+        Cd = np.empty(max(self.c_dense, 1), np.float32)
+        _check(lib().gato_unpack(self._h, _f(G_val), _f(C_val), rho, _f(Gd), _f(Cd)))
+        return Gd, Cd[: self.c_dense]
+
+    def solve_debug(self, G_val, C_val, g, c, exit_tol=1e-6, max_iters=500, rho=0.0):
+        G_val = _f32(G_val, (self.nnzG,)); C_val = _f32(C_val, (self.nnzC,))
+        g = _f32(g, (self.n_z,)); c = _f32(c, (self.n_l,))
+        lam = np.empty(self.n_l, np.float32); dz = np.empty(self.n_z, np.float32)
+        nS = 3 * self.S * self.S * self.K
+        S_ = np.empty(nS, np.float32); P_ = np.empty(nS, np.float32)
+        gam = np.empty(self.n_l, np.float32); Gi = np.empty(self.g_dense, np.float32)
+        it = C.c_int()
+        _check(lib().gato_solve_debug(self._h, _f(G_val), _f(C_val), _f(g), _f(c), _f(lam), _f(dz), exit_tol,
+                                      int(max_iters), rho, C.byref(it), _f(S_), _f(P_), _f(gam), _f(Gi)))
+        return dict(lam=lam, dz=dz, iters=it.value, S=S_, Pinv=P_, gamma=gam, Ginv=Gi)
+
+
+# ------------------------------------------------------------------------------------------------
+# Host-side mirror of gpu_library.linsys_solve for runtime-chosen sizes
+# ------------------------------------------------------------------------------------------------
+_plan_cache: dict = {}
+last_info: dict = {}
+
+
+def _cached_plan(S, C_, K, G_row, G_col, C_row, C_col, device=0):
+    gr = np.ascontiguousarray(G_row, np.int32); gc = np.ascontiguousarray(G_col, np.int32)
+    cr = np.ascontiguousarray(C_row, np.int32); cc = np.ascontiguousarray(C_col, np.int32)
+    key = (S, C_, K, device, gr.tobytes(), gc.tobytes(), cr.tobytes(), cc.tobytes())
+    pl = _plan_cache.get(key)
+    if pl is None:
+        if len(_plan_cache) >= 8:
+            _plan_cache.pop(next(iter(_plan_cache))).close()
+        pl = _plan_cache[key] = Plan(S, C_, K, gr, gc, cr, cc, device=device)
+    return pl
+
+
+def linsys_solve(G_row, G_col, G_val, C_row, C_col, C_val, g_val, c_val, input_lambda, testiters, exit_tol,
+                 max_iters, warm_start, rho, *, S, C, K, true_warm_start=False, device=0):
+    """Same positional arguments, meaning and return value as the reference's
+    `gpu_library.linsys_solve` (gpu_library.cu:85-87, 221-231): -> (list lambda, list dz).
+    The compile-time knobs become the keyword-only S, C, K.  `warm_start=True` has no numerical
+    effect unless `true_warm_start=True` (the reference ignores it, src/gato_pcg.cuh:300-304)."""
+    if testiters < 1:
+        raise ValueError("testiters must be >= 1")
+    pl = _cached_plan(S, C, K, G_row, G_col, C_row, C_col, device)
+    lam_in = np.asarray(input_lambda, np.float32)
+    if lam_in.size < pl.n_l:
+        raise ValueError(f"input_lambda has {lam_in.size} entries, expected {pl.n_l}")
+    warm = WARM_OFF if not warm_start else (WARM_TRUE if true_warm_start else WARM_REFERENCE)
+    times = []
+    for _ in range(testiters):
+        lam, dz, info = pl.solve(G_val, C_val, g_val, c_val, lam_in[: pl.n_l], exit_tol, max_iters, warm, rho)
+        times.append(info["device_ms"])
+    last_info.clear()
+    last_info.update(iters=info["iters"], first_ms=times[0], avg_ms=float(np.mean(times)))
+    return [float(x) for x in lam], [float(x) for x in dz]

@@ -1,0 +1,115 @@
+/* gato_b200.h -- C ABI of the B200-native GATO KKT linear-system hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  Every entry point
+ * cites the reference interface (relative to /root/reference) that it replaces.  All entry points
+ * return 0 on success or a negative GATO_E* / positive cudaError_t code; they never call exit()
+ * (the reference's gpuErrchk does, include/gato_defines.h:42-51).  gato_last_error() returns a
+ * thread-local description of the last failure.
+ *
+ * Data conventions: FP32 values, int32 indices, CSR in SciPy order
+ * (row = indptr, col = indices, val = data); g / dz have (S+C)K-C entries laid out per knot as
+ * [x(S) | u(C)] (last knot x only); c / lambda have S*K entries.
+ */
+#ifndef GATO_B200_H_
+#define GATO_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GATO_OK 0
+#define GATO_EINVAL (-1)      /* bad argument / size mismatch                                  */
+#define GATO_EPATTERN (-2)    /* CSR pattern has entries the block layout cannot hold          */
+#define GATO_EUNSUPPORTED (-3)/* (S, C) not compiled in, or K too large for one cluster        */
+#define GATO_ENODEVICE (-4)   /* no CUDA device / driver: there is NO CPU fallback              */
+
+/* warm_start modes for the solve entry points */
+#define GATO_WARM_OFF 0        /* lambda_in ignored                                             */
+#define GATO_WARM_REFERENCE 1  /* what the reference does with warm_start=True: lambda_in is
+                                  accepted and has NO numerical effect (src/gato_pcg.cuh:300-304) */
+#define GATO_WARM_TRUE 2       /* extension: r0 = gamma - S*lambda_in                            */
+
+typedef struct gato_plan gato_plan; /* opaque: sparsity pattern maps + persistent device workspace */
+
+/* Which (STATE_SIZE, CONTROL_SIZE) pairs this build of the library carries kernels for.
+ * Replaces the compile-time knobs of CMakeLists.txt:18 / install.bash:4-19 at library level; the
+ * pybind11 module `gpu_library` still fixes S, C, K at compile time.  Returns the number of pairs;
+ * writes up to `cap` pairs into sizes[2*i], sizes[2*i+1]. */
+int gato_supported_sizes(int* sizes, int cap);
+
+const char* gato_last_error(void);
+int gato_device_count(void);
+
+/* Build a plan for one sparsity pattern on CUDA device `device`.
+ * Replaces the per-call index arithmetic of csr_to_custom_G / csr_to_custom_C
+ * (src/gato_schur.cuh:674-743) by a one-off host pass that turns each CSR non-zero into its
+ * destination inside the per-knot dense block, and the per-call cudaMalloc/cudaFree of
+ * gato_linsys (gpu_library.cu:36-45, 74-81) and main_call (gpu_library.cu:140-157, 211-218) by a
+ * persistent workspace sized for `max_batch` systems.  Host pointers. */
+int gato_plan_create(int S, int C, int K,
+                     const int* G_row, const int* G_col, int nnzG,
+                     const int* C_row, const int* C_col, int nnzC,
+                     int device, int max_batch, gato_plan** plan_out);
+void gato_plan_destroy(gato_plan* plan);
+
+/* Cluster shape override for tuning: `cluster_ctas` CTAs per system (0 = automatic). */
+int gato_plan_set_cluster(gato_plan* plan, int cluster_ctas);
+int gato_plan_get_cluster(const gato_plan* plan, int* cluster_ctas, int* knots_per_cta);
+
+/* One KKT solve, HOST buffers in and out.  Replaces main_call + gato_linsys
+ * (gpu_library.cu:25-83, 85-231): H2D of values, one fused kernel, D2H of lambda and dz.
+ * lambda_in may be NULL unless warm_start == GATO_WARM_TRUE.  iters_out (may be NULL) receives the
+ * count the reference only prints (gpu_library.cu:189-191): the 0-based index of the iteration
+ * that met |r^T P^-1 r| < exit_tol, or max_iters.  device_ms_out (may be NULL) receives the CUDA
+ * event time of H2D + kernel + D2H (the reference's timed bracket, gpu_library.cu:172-187). */
+int gato_solve(gato_plan* plan,
+               const float* G_val, const float* C_val, const float* g, const float* c,
+               const float* lambda_in, float* lambda_out, float* dz_out,
+               float exit_tol, int max_iters, int warm_start, float rho,
+               int* iters_out, float* device_ms_out);
+
+/* Batch of `nsys` independent systems over the plan's pattern, HOST buffers.  ld* are element
+ * strides between consecutive systems; ld == 0 means the array is shared by all systems.
+ * lambda_out is [nsys][S*K], dz_out is [nsys][(S+C)K-C], iters_out is [nsys] (may be NULL).
+ * The reference has no batched entry point (gpu_library.cu:236-239 exports one function); this is
+ * what a loop over linsys_solve would compute. */
+int gato_solve_batched(gato_plan* plan, int nsys,
+                       const float* G_val, long long ldG, const float* C_val, long long ldC,
+                       const float* g, long long ldg, const float* c, long long ldc,
+                       const float* lambda_in, long long ldl,
+                       float* lambda_out, float* dz_out, int* iters_out,
+                       float exit_tol, int max_iters, int warm_start, float rho,
+                       float* device_ms_out);
+
+/* Same, DEVICE buffers on the plan's device, asynchronous on `stream` (a cudaStream_t passed as
+ * void*; NULL = legacy default stream, which is what the reference uses, include/gato_defines.h:22).
+ * No allocation, no host synchronisation.  Replaces the internal seam gato_linsys
+ * (gpu_library.cu:25-30), whose CSR/g/c arguments are device pointers. */
+int gato_solve_batched_device(gato_plan* plan, int nsys,
+                              const float* dG_val, long long ldG, const float* dC_val, long long ldC,
+                              const float* dg, long long ldg, const float* dc, long long ldc,
+                              const float* dlambda_in, long long ldl,
+                              float* dlambda_out, float* ddz_out, int* diters_out,
+                              float exit_tol, int max_iters, int warm_start, float rho,
+                              void* stream);
+
+/* CSR -> per-knot dense blocks only, HOST buffers (parity hook for gato_convert_kkt_format,
+ * src/gato_schur.cuh:745-756).  G_dense_out has (S^2+C^2)K-C^2 floats, C_dense_out has
+ * (S^2+SC)(K-1) floats, both in the reference's layout (include/gato_defines.h:36-37). */
+int gato_unpack(gato_plan* plan, const float* G_val, const float* C_val, float rho,
+                float* G_dense_out, float* C_dense_out);
+
+/* Solve one system and also return the Schur-phase intermediates in the reference's device layout
+ * and (negated) storage signs: S_out, Pinv_out 3*S^2*K floats (gpu_library.cu:40-41), gamma_out
+ * S*K floats, Ginv_out (S^2+C^2)K-C^2 floats (what form_schur leaves in d_G_dense,
+ * src/gato_schur.cuh:238-259).  Any of the four may be NULL.  Parity hook only. */
+int gato_solve_debug(gato_plan* plan,
+                     const float* G_val, const float* C_val, const float* g, const float* c,
+                     float* lambda_out, float* dz_out,
+                     float exit_tol, int max_iters, float rho, int* iters_out,
+                     float* S_out, float* Pinv_out, float* gamma_out, float* Ginv_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GATO_B200_H_ */
