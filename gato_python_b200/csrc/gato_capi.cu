@@ -162,7 +162,7 @@ int unpack_sc(const gato_plan* pl, const float* dG, const float* dC, float* Gd, 
     return GATO_OK;
 }
 
-#define GATO_FOR_SIZES(X) X(2, 1) X(14, 7)
+#define GATO_FOR_SIZES(X) X(2, 1) X(4, 2) X(7, 3) X(14, 7)
 
 bool size_supported(int S, int C) {
 #define X(s, c) if (S == s && C == c) return true;

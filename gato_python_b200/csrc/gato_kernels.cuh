@@ -46,6 +46,7 @@ struct SolveParams {
     float* eta_out;                      // [nsys] last |r^T P^-1 r| (may be null)
     // --- optional dumps of the Schur phase, reference layout + reference (negated) signs ---
     float* dbg_S; float* dbg_P; float* dbg_gamma; float* dbg_Ginv;
+    long long* dbg_clk;                  // [16] globaltimer ns at phase boundaries (system 0, rank 0), or null
     int K, nsys, max_iters, warm;        // warm: 0/1 = reference behaviour (lambda_in ignored), 2 = true warm start
     float rho, exit_tol;
 };
@@ -77,6 +78,14 @@ struct Layout {
         return kpc * KN + 2 * (kpc + 2) * S + 4 * S + (kpc + 1) * S + 2 * cl * kpc + PREV + 8;
     }
 };
+
+__device__ __forceinline__ void stamp(const SolveParams& p, int slot) {
+    if (p.dbg_clk != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+        long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        p.dbg_clk[slot] = t;
+    }
+}
 
 __device__ __forceinline__ float half_sum16(float v) {
     // butterfly inside each 16-lane half; every lane of the half ends with the same bits
@@ -178,8 +187,10 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
     const int nred = CL * kpc;
     const int nfloats = L::cta_floats(kpc, CL);
 
+    stamp(p, 0);
     for (int i = threadIdx.x; i < nfloats; i += blockDim.x) smem[i] = 0.f;
     __syncthreads();
+    stamp(p, 1);
 
     const float* Gv = p.G_val + (long long)sys * p.ldG;
     const float* Cv = p.C_val + (long long)sys * p.ldC;
@@ -194,6 +205,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
         if (lane < C && b < K - 1) kn[L::or_ + lane] = __ldg(gv + b * (S + C) + S + lane);
     }
     __syncwarp();
+    stamp(p, 2);
 
     // ==== 2. invert Q_b (half 0) and R_b (half 1) in registers ================================
     if (active) {
@@ -216,6 +228,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
                 if (j < D) dst[j * ld + r] = a[j];
         }
     }
+    stamp(p, 3);
     cluster.sync();   // ---- (B1) every stage's A, B, Q^-1, R^-1, q, r are in shared memory
 
     // ==== 3. block row b: phi, gamma, theta, theta^-1 ==========================================
@@ -326,6 +339,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
             }
         }
     }
+    stamp(p, 4);
     cluster.sync();   // ---- (B2) phi_b, theta_b^-1, gamma_b of every block row are in shared memory
 
     // ==== 4. stair left block: PL_b = theta_b^-1 phi_b theta_{b-1}^-1  (P^-1[b,left] = -PL_b) ==
@@ -376,6 +390,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
     } else if (active) {   // b == 0: PL region held BR scratch for nobody; make sure it is zero
         for (int i = lane; i < SS; i += 32) kn[L::oPL + i] = 0.f;
     }
+    stamp(p, 5);
     cluster.sync();   // ---- (B3) every PL_b is in shared memory
 
     // ==== 5. pull this lane's half block-rows of S and P^-1 into registers =====================
@@ -452,6 +467,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
     const bool haloR = warp == kpc - 1 && h == 1 && rowS;
     const int slot = rank * kpc + warp;
 
+    stamp(p, 6);
     // ==== 6. PCG (src/gato_pcg.cuh:270-439) =====================================================
     float lam = 0.f, rr = 0.f, pp = 0.f;
     if (p.warm == 2) {   // opt-in true warm start: r0 = gamma - S lambda0
@@ -489,6 +505,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
 
     int iters = p.max_iters;
     float eta_last = eta;
+    stamp(p, 7);
     for (int it = 0; it < p.max_iters; ++it) {
         const float ups = matvec(Srow, xp);
         {
@@ -528,6 +545,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
         __syncthreads();
     }
 
+    stamp(p, 8);
     // ==== 7. dz = G^-1 (g - C^T lambda)  (src/gato_schur.cuh:759-867) ===========================
     if (own) lamh[warp * S + r] = lam;
     if (pushL) nbL[o_lamh + kpc * S + r] = lam;
@@ -565,6 +583,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
             dz[S + r] = acc;
         }
     }
+    stamp(p, 9);
     if (rank == 0 && threadIdx.x == 0) {
         p.iters_out[sys] = iters;
         if (p.eta_out != nullptr) p.eta_out[sys] = fabsf(eta_last);

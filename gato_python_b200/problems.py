@@ -169,3 +169,42 @@ def iiwa_like_batch(nsys, S=14, C=7, K=50, seed0=1000, preset="stiff", dt=0.01, 
         gg[i], cc[i] = g, c
     return dict(S=S, C=C, K=K, nsys=nsys, G_row=G_row, G_col=G_col, G_val=GV, C_row=C_row,
                 C_col=C_col, C_val=CV, g=gg, c=cc, exit_tol=exit_tol, max_iters=max_iters, rho=rho)
+
+
+def iiwa_like_batch_fast(nsys, S=14, C=7, K=50, seed=1000, preset="stiff", dt=0.01, rho=1e-3, exit_tol=1e-6,
+                         max_iters=500, first=0):
+    """Vectorised batch generator for benchmarks: the same model as `iiwa_like` (diagonal G, structural
+    A/B sparsity) drawn for all systems at once.  System i depends only on (seed, first + i), so a
+    shard [first, first + nsys) of a larger batch is reproducible on its own."""
+    G_row, G_col, g_src, C_row, C_col, c_src, Amask, Bmask = _pattern(S, C, K, False, False)
+    h = S // 2
+    q_pos, q_vel, rr, q_N = _PRESETS[preset]
+    n_z, n_l = (S + C) * K - C, S * K
+    GV = np.empty((nsys, len(G_col)), np.float32)
+    CV = np.empty((nsys, len(C_col)), np.float32)
+    gg = np.empty((nsys, n_z), np.float32)
+    cc = np.empty((nsys, n_l), np.float32)
+    kind, k, r, c = g_src.T
+    gdiag = np.where(kind == 0, np.where(r < h, q_pos, q_vel) * np.where(k == K - 1, q_N, 1.0), rr)
+    GV[:] = gdiag.astype(np.float32)
+    ck, kk, cr, ccol = c_src.T
+    mA, mB, mI = ck == 2, ck == 3, ck == 4
+    chunk = 256
+    for s0 in range(0, nsys, chunk):
+        n = min(chunk, nsys - s0)
+        rng = np.random.default_rng([seed, first + s0])
+        A = np.tile(np.eye(S), (n, K - 1, 1, 1))
+        A[:, :, :h, h:2 * h] += dt * np.eye(h)
+        A[:, :, h:, :] += dt * rng.standard_normal((n, K - 1, S - h, S))
+        B = np.zeros((n, K - 1, S, C))
+        eyeB = np.zeros((S - h, C)); m = min(S - h, C); eyeB[:m, :m] = np.eye(m)
+        B[:, :, h:, :] = dt * (2.0 * eyeB + 0.3 * rng.standard_normal((n, K - 1, S - h, C)))
+        cv = CV[s0:s0 + n]
+        cv[:, mA] = -A[:, kk[mA], cr[mA], ccol[mA]]
+        cv[:, mB] = -B[:, kk[mB], cr[mB], ccol[mB]]
+        cv[:, mI] = 1.0
+        gg[s0:s0 + n] = rng.standard_normal((n, n_z))
+        cx = 0.01 * rng.standard_normal((n, n_l)); cx[:, :S] = 0.0
+        cc[s0:s0 + n] = cx
+    return dict(S=S, C=C, K=K, nsys=nsys, G_row=G_row, G_col=G_col, G_val=GV, C_row=C_row, C_col=C_col,
+                C_val=CV, g=gg, c=cc, exit_tol=exit_tol, max_iters=max_iters, rho=rho)

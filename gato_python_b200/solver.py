@@ -59,7 +59,7 @@ def lib():
         [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_float, C.c_void_p]
     L.gato_unpack.argtypes = [C.c_void_p, _fp, _fp, C.c_float, _fp, _fp]
     L.gato_solve_debug.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_float,
-                                   _ip, _fp, _fp, _fp, _fp]
+                                   _ip, _fp, _fp, _fp, _fp, C.POINTER(C.c_longlong)]
     _lib = L
     return L
 
@@ -205,9 +205,11 @@ class Plan:
         S_ = np.empty(nS, np.float32); P_ = np.empty(nS, np.float32)
         gam = np.empty(self.n_l, np.float32); Gi = np.empty(self.g_dense, np.float32)
         it = C.c_int()
+        clk = np.zeros(16, np.int64)
         _check(lib().gato_solve_debug(self._h, _f(G_val), _f(C_val), _f(g), _f(c), _f(lam), _f(dz), exit_tol,
-                                      int(max_iters), rho, C.byref(it), _f(S_), _f(P_), _f(gam), _f(Gi)))
-        return dict(lam=lam, dz=dz, iters=it.value, S=S_, Pinv=P_, gamma=gam, Ginv=Gi)
+                                      int(max_iters), rho, C.byref(it), _f(S_), _f(P_), _f(gam), _f(Gi),
+                                      clk.ctypes.data_as(C.POINTER(C.c_longlong))))
+        return dict(lam=lam, dz=dz, iters=it.value, S=S_, Pinv=P_, gamma=gam, Ginv=Gi, clk_ns=clk)
 
 
 # ------------------------------------------------------------------------------------------------

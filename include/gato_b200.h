@@ -102,12 +102,16 @@ int gato_unpack(gato_plan* plan, const float* G_val, const float* C_val, float r
 /* Solve one system and also return the Schur-phase intermediates in the reference's device layout
  * and (negated) storage signs: S_out, Pinv_out 3*S^2*K floats (gpu_library.cu:40-41), gamma_out
  * S*K floats, Ginv_out (S^2+C^2)K-C^2 floats (what form_schur leaves in d_G_dense,
- * src/gato_schur.cuh:238-259).  Any of the four may be NULL.  Parity hook only. */
+ * src/gato_schur.cuh:238-259).  clk_ns_out (16 entries) receives %globaltimer stamps of the
+ * kernel's phase boundaries: 0 start, 1 smem cleared, 2 unpacked, 3 Q/R inverted, 4 Schur rows
+ * formed, 5 stair blocks formed, 6 rows in registers, 7 PCG loop start, 8 PCG loop end, 9 dz
+ * written.  Any of the five may be NULL.  Parity / profiling hook only. */
 int gato_solve_debug(gato_plan* plan,
                      const float* G_val, const float* C_val, const float* g, const float* c,
                      float* lambda_out, float* dz_out,
                      float exit_tol, int max_iters, float rho, int* iters_out,
-                     float* S_out, float* Pinv_out, float* gamma_out, float* Ginv_out);
+                     float* S_out, float* Pinv_out, float* gamma_out, float* Ginv_out,
+                     long long* clk_ns_out);
 
 #ifdef __cplusplus
 }
