@@ -152,8 +152,10 @@ class Plan:
 
     # -- batch, host buffers ---------------------------------------------------------------------
     def solve_batched(self, G_val, C_val, g, c, lambda_in=None, exit_tol=1e-6, max_iters=500,
-                      warm_start=WARM_OFF, rho=0.0):
-        """Arrays are [nsys, n] or [n] (shared by all systems).  -> (lambda, dz, iters, device_ms)"""
+                      warm_start=WARM_OFF, rho=0.0, out=None):
+        """Arrays are [nsys, n] or [n] (shared by all systems).  -> (lambda, dz, iters, device_ms)
+        `out=(lambda, dz, iters)`: preallocated float32/float32/int32 result arrays (e.g. views of
+        pinned host memory, which makes the D2H copies asynchronous)."""
         g = np.ascontiguousarray(g, np.float32)
         if g.ndim != 2 or g.shape[1] != self.n_z:
             raise ValueError(f"g must be [nsys, {self.n_z}]")
@@ -171,9 +173,16 @@ class Plan:
         C_val, ldC = prep(C_val, self.nnzC)
         c, ldc = prep(c, self.n_l)
         lam_in, ldl = (prep(lambda_in, self.n_l) if lambda_in is not None else (None, 0))
-        lam = np.empty((nsys, self.n_l), np.float32)
-        dz = np.empty((nsys, self.n_z), np.float32)
-        iters = np.empty(nsys, np.int32)
+        if out is None:
+            lam = np.empty((nsys, self.n_l), np.float32)
+            dz = np.empty((nsys, self.n_z), np.float32)
+            iters = np.empty(nsys, np.int32)
+        else:
+            lam, dz, iters = out
+            for a, shp, dt in ((lam, (nsys, self.n_l), np.float32), (dz, (nsys, self.n_z), np.float32),
+                               (iters, (nsys,), np.int32)):
+                if a.shape != shp or a.dtype != dt or not a.flags.c_contiguous:
+                    raise ValueError(f"out array must be C-contiguous {shp} {np.dtype(dt).name}")
         ms = C.c_float()
         _check(lib().gato_solve_batched(self._h, nsys, _f(G_val), ldG, _f(C_val), ldC, _f(g), self.n_z,
                                         _f(c), ldc, _f(lam_in) if lam_in is not None else None, ldl,

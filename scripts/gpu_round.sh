@@ -1,0 +1,16 @@
+#!/bin/bash
+# One GPU-box pass: parity tests, bench (ours + reference), ncu launch list + full capture of the fused kernel.
+set -u
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+python bench.py --steps 10 --warmup 3 > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err; echo "bench rc=$?"
+tail -c 3000 gpurun_out/bench_ours.json
+python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
+tail -c 1500 gpurun_out/bench_ref.json
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-single"
+$CMD > gpurun_out/plain.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+echo "ncu launches rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:gato_fused -s 3 -c 1 -o gpurun_out/prof_fused $CMD > gpurun_out/ncu_full.log 2>&1
+echo "ncu full rc=$?"
+ls -la gpurun_out
