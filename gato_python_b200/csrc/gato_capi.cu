@@ -12,6 +12,7 @@
 
 #include "../../include/gato_b200.h"
 #include "gato_kernels.cuh"
+#include "gato_kernel_v2.cuh"
 
 #ifndef GATO_EXTRA_S
 #define GATO_EXTRA_S 0
@@ -77,10 +78,13 @@ struct gato_plan {
     int S, C, K, nnzG, nnzC, device, max_batch;
     int n_z, n_l, g_dense, c_dense;
     int cl_override = 0;
+    int kernel = 0;         // 0 = automatic, 1 = cluster kernel (v1), 2 = one-CTA-per-system kernel (v2)
+    int g_diag = 0;         // G's pattern is purely diagonal
     int sm_count = 0;
     int smem_optin = 0;
     // device: pattern maps
     int *d_gmap = nullptr, *d_cmap = nullptr, *d_gstart = nullptr, *d_cstart = nullptr;
+    int *d_gdst2 = nullptr, *d_cdst2 = nullptr;   // v2: absolute shared-memory destinations
     // device: staged inputs / outputs for the host-buffer entry points
     DevBuf dG, dC, dg, dc, dl, dlo, ddz, dit, dbg;
     PinBuf hin, hout;   // pinned staging for the single-solve path
@@ -162,6 +166,58 @@ int unpack_sc(const gato_plan* pl, const float* dG, const float* dC, float* Gd, 
     return GATO_OK;
 }
 
+
+// ---- v2: one CTA per system ---------------------------------------------------------------------
+// thread-count menu per state size: ptxas gets 65536 / NT registers per thread, so NT bounds the
+// number of knots (8 lanes each) one CTA can hold
+template <int S> struct V2Menu { static constexpr int n = 3; static constexpr int nt[3] = {64, 256, 1024}; };
+template <> struct V2Menu<14> { static constexpr int n = 3; static constexpr int nt[3] = {64, 128, 224}; };
+
+template <int S, int C>
+int v2_pick_nt(const gato_plan* pl) {   // smallest menu entry that holds K knots and fits shared memory; 0 = none
+    using L = gato::Layout2<S, C>;
+    for (int i = 0; i < V2Menu<S>::n; ++i) {
+        const int nt = V2Menu<S>::nt[i];
+        if (nt >= L::LPK * pl->K && (size_t)L::smem_floats(pl->K, nt) * 4 <= (size_t)pl->smem_optin) return nt;
+    }
+    return 0;
+}
+
+template <int S, int C, int NT>
+int launch_v2_t(const gato::SolveParams2& q, cudaStream_t st) {
+    using L = gato::Layout2<S, C>;
+    auto kern = gato::gato_fused_solve_v2<S, C, NT>;
+    const size_t smem = (size_t)L::smem_floats(q.p.K, NT) * 4;
+    GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)q.p.nsys, NT, smem, st>>>(q);
+    GATO_CUDA(cudaGetLastError());
+    return GATO_OK;
+}
+
+template <int S, int C>
+int launch_v2_sc(const gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
+    const int nt = v2_pick_nt<S, C>(pl);
+    if (nt == V2Menu<S>::nt[0]) return launch_v2_t<S, C, V2Menu<S>::nt[0]>(q, st);
+    if (nt == V2Menu<S>::nt[1]) return launch_v2_t<S, C, V2Menu<S>::nt[1]>(q, st);
+    if constexpr (V2Menu<S>::n > 2) {
+        if (nt == V2Menu<S>::nt[2]) return launch_v2_t<S, C, V2Menu<S>::nt[2]>(q, st);
+    }
+    return fail(GATO_EUNSUPPORTED, "K=%d does not fit the one-CTA kernel", pl->K);
+}
+
+template <int S, int C>
+void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::vector<int>& gstart,
+                  const std::vector<int>& cmap, const std::vector<int>& cstart, std::vector<int>* gdst,
+                  std::vector<int>* cdst) {
+    using L = gato::Layout2<S, C>;
+    for (int k = 0; k < pl->K; ++k) {
+        for (int t = gstart[k]; t < gstart[k + 1]; ++t)
+            (*gdst)[t] = (k * L::KN + L::oQ + (gmap[t] & gato::kMapMask)) | (gmap[t] & gato::kMapDiagBit);
+        for (int t = cstart[k]; t < cstart[k + 1]; ++t)
+            (*cdst)[t] = cmap[t] < 0 ? -1 : k * L::KN + L::oA + cmap[t];
+    }
+}
+
 #define GATO_FOR_SIZES(X) X(2, 1) X(4, 2) X(7, 3) X(14, 7)
 
 bool size_supported(int S, int C) {
@@ -206,6 +262,44 @@ int cfg_for(const gato_plan* pl, LaunchCfg* cfg) {
         return pick_cfg<GATO_EXTRA_S, GATO_EXTRA_C>(pl, cfg);
 #endif
     return fail(GATO_EUNSUPPORTED, "no kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+
+int v2_nt_for(const gato_plan* pl) {
+#define X(s, c) if (pl->S == s && pl->C == c) return v2_pick_nt<s, c>(pl);
+    GATO_FOR_SIZES(X)
+#undef X
+    return 0;
+}
+
+bool use_v2(const gato_plan* pl) {
+    if (pl->kernel == 1 || (pl->kernel == 0 && pl->cl_override > 0)) return false;
+    return v2_nt_for(pl) > 0;
+}
+
+int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+    gato::SolveParams2 q;
+    q.p = p;
+    q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
+#define X(s, c) if (pl->S == s && pl->C == c) return launch_v2_sc<s, c>(pl, q, st);
+    GATO_FOR_SIZES(X)
+#undef X
+    return fail(GATO_EUNSUPPORTED, "no v2 kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+void v2_maps_for(const gato_plan* pl, const std::vector<int>& gmap, const std::vector<int>& gstart,
+                 const std::vector<int>& cmap, const std::vector<int>& cstart, std::vector<int>* gdst,
+                 std::vector<int>* cdst) {
+#define X(s, c) if (pl->S == s && pl->C == c) return v2_fill_maps<s, c>(pl, gmap, gstart, cmap, cstart, gdst, cdst);
+    GATO_FOR_SIZES(X)
+#undef X
+}
+
+// the kernel the plan selects; dumps of the Schur intermediates exist only in the cluster kernel
+int launch_auto(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+    if (p.dbg_S == nullptr && use_v2(pl)) return launch_solve_v2(pl, p, st);
+    return launch_solve(pl, p, st);
 }
 
 }  // namespace

@@ -19,7 +19,8 @@ WARM_OFF, WARM_REFERENCE, WARM_TRUE = 0, 1, 2
 #: every symbol include/gato_b200.h declares
 SYMBOLS = [
     "gato_supported_sizes", "gato_last_error", "gato_device_count", "gato_plan_create",
-    "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_solve",
+    "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel",
+    "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
 
@@ -51,6 +52,8 @@ def lib():
     L.gato_plan_destroy.restype = None
     L.gato_plan_set_cluster.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_get_cluster.argtypes = [C.c_void_p, _ip, _ip]
+    L.gato_plan_set_kernel.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_get_kernel.argtypes = [C.c_void_p]
     L.gato_solve.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_int,
                              C.c_float, _ip, _fp]
     L.gato_solve_batched.argtypes = [C.c_void_p, C.c_int, _fp, _ll, _fp, _ll, _fp, _ll, _fp, _ll, _fp, _ll,
@@ -130,6 +133,13 @@ class Plan:
     def set_cluster(self, cluster_ctas):
         _check(lib().gato_plan_set_cluster(self._h, int(cluster_ctas)))
 
+    def set_kernel(self, kernel):
+        """0 = automatic, 1 = cluster kernel, 2 = one-CTA-per-system kernel."""
+        _check(lib().gato_plan_set_kernel(self._h, int(kernel)))
+
+    def kernel(self):
+        return lib().gato_plan_get_kernel(self._h)
+
     def cluster(self):
         a, b = C.c_int(), C.c_int()
         _check(lib().gato_plan_get_cluster(self._h, C.byref(a), C.byref(b)))
@@ -206,17 +216,25 @@ class Plan:
         _check(lib().gato_unpack(self._h, _f(G_val), _f(C_val), rho, _f(Gd), _f(Cd)))
         return Gd, Cd[: self.c_dense]
 
-    def solve_debug(self, G_val, C_val, g, c, exit_tol=1e-6, max_iters=500, rho=0.0):
+    def solve_debug(self, G_val, C_val, g, c, exit_tol=1e-6, max_iters=500, rho=0.0, dumps=True):
+        """Solve + phase time stamps.  `dumps=True` also returns the Schur intermediates in the
+        reference's layout (this forces the cluster kernel, the only one that can dump them);
+        `dumps=False` profiles whichever kernel the plan selects."""
         G_val = _f32(G_val, (self.nnzG,)); C_val = _f32(C_val, (self.nnzC,))
         g = _f32(g, (self.n_z,)); c = _f32(c, (self.n_l,))
         lam = np.empty(self.n_l, np.float32); dz = np.empty(self.n_z, np.float32)
         nS = 3 * self.S * self.S * self.K
-        S_ = np.empty(nS, np.float32); P_ = np.empty(nS, np.float32)
-        gam = np.empty(self.n_l, np.float32); Gi = np.empty(self.g_dense, np.float32)
         it = C.c_int()
         clk = np.zeros(16, np.int64)
+        if dumps:
+            S_ = np.empty(nS, np.float32); P_ = np.empty(nS, np.float32)
+            gam = np.empty(self.n_l, np.float32); Gi = np.empty(self.g_dense, np.float32)
+            ptrs = (_f(S_), _f(P_), _f(gam), _f(Gi))
+        else:
+            S_ = P_ = gam = Gi = None
+            ptrs = (None, None, None, None)
         _check(lib().gato_solve_debug(self._h, _f(G_val), _f(C_val), _f(g), _f(c), _f(lam), _f(dz), exit_tol,
-                                      int(max_iters), rho, C.byref(it), _f(S_), _f(P_), _f(gam), _f(Gi),
+                                      int(max_iters), rho, C.byref(it), *ptrs,
                                       clk.ctypes.data_as(C.POINTER(C.c_longlong))))
         return dict(lam=lam, dz=dz, iters=it.value, S=S_, Pinv=P_, gamma=gam, Ginv=Gi, clk_ns=clk)
 

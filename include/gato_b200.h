@@ -56,6 +56,14 @@ void gato_plan_destroy(gato_plan* plan);
 int gato_plan_set_cluster(gato_plan* plan, int cluster_ctas);
 int gato_plan_get_cluster(const gato_plan* plan, int* cluster_ctas, int* knots_per_cta);
 
+/* Kernel selection for tuning and tests: 0 = automatic, 1 = cluster kernel (one thread-block cluster
+ * per system, DSMEM exchange; any K up to 16 CTAs x 32 knots), 2 = one-CTA-per-system kernel (whole
+ * system resident in one SM's registers, block barriers only; the batched path and the default
+ * whenever K fits).  Both replace the same reference functions (parallelPCG, src/gato_pcg.cuh:441-470,
+ * and the three Schur/dz kernels, src/gato_schur.cuh:462-494, 652-670, 869-879). */
+int gato_plan_set_kernel(gato_plan* plan, int kernel);
+int gato_plan_get_kernel(const gato_plan* plan);
+
 /* One KKT solve, HOST buffers in and out.  Replaces main_call + gato_linsys
  * (gpu_library.cu:25-83, 85-231): H2D of values, one fused kernel, D2H of lambda and dz.
  * lambda_in may be NULL unless warm_start == GATO_WARM_TRUE.  iters_out (may be NULL) receives the

@@ -82,10 +82,17 @@ def test_unpack_bit_exact(name):
     pl.close()
 
 
+@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
 @pytest.mark.parametrize("name", list(CASES))
-def test_solve_vs_oracle(name):
+def test_solve_vs_oracle(name, kernel):
     prob = CASES[name]()
     pl = plan_of(prob)
+    try:
+        pl.set_kernel(kernel)
+    except solver.GatoError:
+        assert kernel == 2 and name in ("iiwa256", "S4_K512_max_cluster")   # beyond one CTA: cluster kernel only
+        pytest.skip("K does not fit the one-CTA kernel")
+    assert pl.kernel() == kernel
     warm = WARM_REFERENCE if "warmflag" in name else 0
     lam_in = np.full(prob["S"] * prob["K"], 3.0, np.float32) if warm else None
     lam, dz, info = gpu(pl, prob, warm=warm, lambda_in=lam_in)
@@ -167,9 +174,11 @@ def test_cluster_shapes_agree(cl):
     pl.close()
 
 
-def test_true_warm_start_extension():
+@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+def test_true_warm_start_extension(kernel):
     prob = CASES["iiwa50_s0"]()
     pl = plan_of(prob)
+    pl.set_kernel(kernel)
     lam, dz, info = gpu(pl, prob)
     lam2, dz2, info2 = gpu(pl, dict(prob, exit_tol=1e-4), warm=WARM_TRUE, lambda_in=lam)
     assert info2["iters"] <= 2 and close(lam2, lam)
@@ -180,9 +189,11 @@ def test_true_warm_start_extension():
     pl.close()
 
 
-def test_edge_cases():
+@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+def test_edge_cases(kernel):
     prob = CASES["iiwa50_s0"]()
     pl = plan_of(prob)
+    pl.set_kernel(kernel)
     lam, dz, info = gpu(pl, dict(prob, max_iters=0))            # src/gato_pcg.cuh:311-313, 348
     assert info["iters"] == 0 and not lam.any()
     lam, dz, info = gpu(pl, dict(prob, max_iters=7))            # not converged: count = max_iters
@@ -196,9 +207,25 @@ def test_edge_cases():
     pl.close()
 
 
-def test_batched_matches_single_and_oracle():
+def test_default_kernel_selection():
+    """K that fits one CTA runs the one-CTA kernel; longer horizons fall back to the cluster kernel."""
+    pl = plan_of(CASES["iiwa50_s0"]())
+    assert pl.kernel() == 2 and pl.cluster() == (1, 50)
+    pl.set_cluster(8)
+    assert pl.kernel() == 1 and pl.cluster()[0] == 8
+    pl.set_cluster(0)
+    assert pl.kernel() == 2
+    pl.close()
+    pl = plan_of(CASES["iiwa256"]())
+    assert pl.kernel() == 1
+    pl.close()
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+def test_batched_matches_single_and_oracle(kernel):
     b = iiwa_like_batch(24, K=50, seed0=1000)
     pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"])
+    pl.set_kernel(kernel)
     lam, dz, iters, ms = pl.solve_batched(b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"],
                                           b["max_iters"], 0, b["rho"])
     for i in (0, 11, 23):
