@@ -209,12 +209,28 @@ template <int S, int C>
 void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::vector<int>& gstart,
                   const std::vector<int>& cmap, const std::vector<int>& cstart, std::vector<int>* gdst,
                   std::vector<int>* cdst) {
+    // gmap / cmap hold the reference's column-major in-block offsets; re-target them to
+    // the v2 shared-memory layout (Layout2: pos-padded rows, Q and R row-major)
     using L = gato::Layout2<S, C>;
     for (int k = 0; k < pl->K; ++k) {
-        for (int t = gstart[k]; t < gstart[k + 1]; ++t)
-            (*gdst)[t] = (k * L::KN + L::oQ + (gmap[t] & gato::kMapMask)) | (gmap[t] & gato::kMapDiagBit);
-        for (int t = cstart[k]; t < cstart[k + 1]; ++t)
-            (*cdst)[t] = cmap[t] < 0 ? -1 : k * L::KN + L::oA + cmap[t];
+        for (int t = gstart[k]; t < gstart[k + 1]; ++t) {
+            const int off = gmap[t] & gato::kMapMask;
+            int dst;
+            if (off < S * S) {
+                const int c = off / S, r = off % S;
+                dst = L::oQ + r * L::VS + L::pos(c);
+            } else {
+                const int c = (off - S * S) / C, r = (off - S * S) % C;
+                dst = L::oR + r * L::LDC + c;
+            }
+            (*gdst)[t] = (k * L::KN + dst) | (gmap[t] & gato::kMapDiagBit);
+        }
+        for (int t = cstart[k]; t < cstart[k + 1]; ++t) {
+            if (cmap[t] < 0) { (*cdst)[t] = -1; continue; }
+            const int col = cmap[t] / S, r = cmap[t] % S;
+            const int dst = col < S ? L::oA + col * L::VS + L::pos(r) : L::oB + (col - S) * L::VS + L::pos(r);
+            (*cdst)[t] = k * L::KN + dst;
+        }
     }
 }
 

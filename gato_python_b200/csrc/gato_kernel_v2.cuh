@@ -41,16 +41,27 @@ struct Layout2 {
     static constexpr int VS = HALFP * H;                       // padded knot stride of the iterates
     static_assert(H == 1 || R == HALFU, "row groups and column halves must split at the same row");
     static_assert(C <= VS, "control vector must fit one iterate slot");
-    // per-knot shared-memory region (floats); [A|B] and [Q|R] contiguous like the reference layout
+    // Per-knot shared-memory region (floats).  Every index that runs over state rows uses the
+    // split-pad position pos(r) with leading dimension VS, so a lane's own rows are one aligned
+    // float4 and a whole column / row is VS/4 float4:
+    //   A   [k < S][VS]   A[r,k]   at k*VS + pos(r)        B    [k < C][VS]  B[r,k] at k*VS + pos(r)
+    //   Q   [r < S][VS]   Q[r,c]   at r*VS + pos(c)  (raw Q, then Q^-1, row-major)
+    //   R   [r < C][LDC]  R[r,c]   at r*LDC + c      (raw R, then R^-1, row-major)
+    //   q   [VS] at pos(r)         r [LDC]
+    //   phi [k < S][VS]   phi[r,k] at k*VS + pos(r)  (block row 0 stashes raw Q0 here, row-major)
+    static constexpr int LDC = (C + 3) & ~3;
     static constexpr int oA = 0;
-    static constexpr int oB = oA + SS;
-    static constexpr int oQ = oB + SC;
-    static constexpr int oR = oQ + SS;
-    static constexpr int oq = oR + CC;
-    static constexpr int or_ = oq + S;
-    static constexpr int oPhi = (or_ + C + 3) & ~3;
-    static constexpr int oTmp = oPhi + SS;
-    static constexpr int KN = (oTmp + SS + 3) & ~3;
+    static constexpr int oB = oA + S * VS;
+    static constexpr int oQ = oB + C * VS;
+    static constexpr int oR = oQ + S * VS;
+    static constexpr int oq = oR + C * LDC;
+    static constexpr int or_ = oq + VS;
+    static constexpr int oPhi = or_ + LDC;
+    static constexpr int KN0 = oPhi + S * VS;
+    // consecutive knots of a warp start 4 banks apart: KPW 16-byte accesses at the same in-knot
+    // offset hit distinct banks
+    static constexpr int KN = ((KN0 - 4 + 31) / 32) * 32 + 4;
+    static constexpr bool VEC_OWN = (OWN == 4);   // own rows = one aligned float4 of positions
 
     // position of row r inside a knot's iterate slot, and back
     __host__ __device__ static constexpr int pos(int r) { return (r / HALFU) * HALFP + (r % HALFU); }
@@ -145,6 +156,7 @@ struct SolveParams2 {
     int g_diag;           // pattern of G is purely diagonal: Q_k^-1, R_k^-1 are reciprocals
 };
 
+
 // NT = threads per CTA (a multiple of 32, >= LPK * K).  The register file is split over the four SM
 // sub-partitions (16 K registers each, warps dealt round-robin), so the cap per thread is
 // 16384 / (32 * ceil(warps / 4)); __launch_bounds__ derives exactly that from NT.
@@ -154,7 +166,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     using MS = MapState<S, C>;
     using MC = MapControl<S, C>;
     constexpr int LPK = L::LPK, OWN = L::OWN, OWNC = L::OWNC, H = L::H, R = L::R, VS = L::VS,
-                  HALFP = L::HALFP, HALFU = L::HALFU, KN = L::KN;
+                  HALFP = L::HALFP, HALFU = L::HALFU, KN = L::KN, LDC = L::LDC;
+    constexpr bool VEC = L::VEC_OWN;
     constexpr int NW = NT / 32, NKP = NW * L::KPW, NW4 = (NW + 3) / 4;
     extern __shared__ __align__(16) float smem[];
     const SolveParams& p = q.p;
@@ -177,16 +190,38 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     float* redB = redA + 32;                           // per-warp partials of r.P^-1r [32]
     const int nfloats = L::smem_floats(K, NT);
 
-    // rows of the iterates (and of the Schur-phase row work) owned by this lane
-    int orow[OWN], po[OWN];
-    bool ov[OWN];
+    // rows of the iterates (and of the Schur-phase row work) owned by this lane: OWN consecutive
+    // positions starting at po0
+    const int po0 = L::own_valid(lik, 0) ? L::pos(L::own_row(lik, 0)) : 0;
+    int orow[OWN];
+    bool ovr[OWN], ov[OWN];
 #pragma unroll
     for (int j = 0; j < OWN; ++j) {
-        const bool valid = L::own_valid(lik, j);
-        orow[j] = valid ? L::own_row(lik, j) : 0;
-        ov[j] = active && valid;
-        po[j] = L::pos(orow[j]);
+        ovr[j] = L::own_valid(lik, j);
+        orow[j] = ovr[j] ? L::own_row(lik, j) : 0;
+        ov[j] = active && ovr[j];
     }
+    auto load_own = [&](const float* base, float (&v)[OWN]) {    // base = a VS-long slot in pos layout
+        if constexpr (VEC) {
+            const float4 t = *reinterpret_cast<const float4*>(base + po0);
+            const float e[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+            for (int j = 0; j < OWN; ++j) v[j] = e[j];           // pad positions hold zeros
+        } else {
+#pragma unroll
+            for (int j = 0; j < OWN; ++j) v[j] = ovr[j] ? base[po0 + j] : 0.f;
+        }
+    };
+    auto store_own = [&](float* base, const float (&v)[OWN]) {   // entries of invalid rows are zero
+        if (!active) return;
+        if constexpr (VEC) {
+            *reinterpret_cast<float4*>(base + po0) = make_float4(v[0], v[1], v[2], v[OWN - 1]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < OWN; ++j)
+                if (ovr[j]) base[po0 + j] = v[j];
+        }
+    };
 
     stamp(p, 0);
     {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0
@@ -202,198 +237,270 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     const float* cv = p.c + (long long)sys * p.ldc;
 
     // ==== 1. unpack: coalesced reads of the CSR values, scatter into the dense per-knot blocks ====
+#pragma unroll 4
     for (int t = tid; t < q.nnzC; t += NT) {
         const int m = __ldg(q.cdst + t);
         const float v = __ldg(Cv + t);
         if (m >= 0) smem[m] = v;
     }
+#pragma unroll 4
     for (int t = tid; t < q.nnzG; t += NT) {
         const int m = __ldg(q.gdst + t);
         const float v = __ldg(Gv + t);
         smem[m & kMapMask] = v + ((m & kMapDiagBit) ? p.rho : 0.0f);
     }
-    {   // g -> per-knot q | r (contiguous in the region)
+    {   // g -> per-knot q (pos layout) | r
         const int n_z = (S + C) * K - C;
+#pragma unroll 4
         for (int t = tid; t < n_z; t += NT) {
             const int k = t / (S + C), o = t - k * (S + C);
-            smem[k * KN + L::oq + o] = __ldg(gv + t);
+            smem[k * KN + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = __ldg(gv + t);
         }
     }
     __syncthreads();
     stamp(p, 2);
 
-    // ==== 2. Q_b^-1 and R_b^-1 (rows spread over the knot's lanes) ================================
-    // The shuffles inside the elimination need the whole warp: lanes without a matrix carry an
-    // identity through it and simply do not store.
-    {
-        float a[OWN][S];
+    // ---- Schur-phase helpers (own-row mapping) -----------------------------------------------------
+    // row `row` of a row-major [.][VS] matrix in pos layout -> registers indexed by true column
+    auto load_row = [&](const float* rowbase, float (&v)[S]) {
 #pragma unroll
-        for (int i = 0; i < OWN; ++i) {
+        for (int ci = 0; ci < VS / 4; ++ci) {
+            const float4 t = reinterpret_cast<const float4*>(rowbase)[ci];
+            const float e[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
-            for (int j = 0; j < S; ++j)
-                a[i][j] = ov[i] ? kn[L::oQ + j * S + orow[i]] : (MS::row(lik, i) == j ? 1.f : 0.f);
+            for (int u = 0; u < 4; ++u)
+                if (L::pos_valid(4 * ci + u)) v[L::pos_row(4 * ci + u)] = e[u];
         }
-        if (b == 0) {   // block row 0 keeps raw Q0 as theta_0^-1 (src/gato_schur.cuh:75-81)
+    };
+    auto store_row = [&](float* rowbase, const float (&v)[S]) {
+#pragma unroll
+        for (int ci = 0; ci < VS / 4; ++ci) {
+            float e[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) e[u] = L::pos_valid(4 * ci + u) ? v[L::pos_row(4 * ci + u)] : 0.f;
+            reinterpret_cast<float4*>(rowbase)[ci] = make_float4(e[0], e[1], e[2], e[3]);
+        }
+    };
+    // out[i][c] += sum_k X[row_i, k] * Y[c, k]:  X = [k][VS] with rows in pos layout (own rows are
+    // one aligned load), Y = [k][VS] with its first index in pos layout (a whole column per k)
+    auto rank1_S = [&](float (&out)[OWN][S], const float* X, const float* Y, int nk) {
+#pragma unroll 1
+        for (int k = 0; k < nk; ++k) {
+            float xv[OWN], yv[S];
+            load_own(X + k * VS, xv);
+            load_row(Y + k * VS, yv);
 #pragma unroll
             for (int i = 0; i < OWN; ++i)
-                if (ov[i]) {
 #pragma unroll
-                    for (int j = 0; j < S; ++j) kn[L::oTmp + j * S + orow[i]] = a[i][j];
-                }
+                for (int c = 0; c < S; ++c) out[i][c] = fmaf(xv[i], yv[c], out[i][c]);
         }
-        if (q.g_diag) {
+    };
+    // same with a C-wide output; Y = [k][LDC] plain
+    auto rank1_C = [&](float (&out)[OWN][C], const float* X, const float* Y, int nk) {
+#pragma unroll 1
+        for (int k = 0; k < nk; ++k) {
+            float xv[OWN];
+            load_own(X + k * VS, xv);
 #pragma unroll
-            for (int i = 0; i < OWN; ++i)
+            for (int c = 0; c < C; ++c) {
+                const float y = Y[k * LDC + c];
 #pragma unroll
-                for (int j = 0; j < S; ++j)
-                    if (MS::row(lik, i) == j) a[i][j] = 1.0f / a[i][j];
-        } else {
-            gj_invert_knot<MS, LPK>(a, lik, lane);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < OWN; ++i)
-            if (ov[i]) {
-#pragma unroll
-                for (int j = 0; j < S; ++j) kn[L::oQ + j * S + orow[i]] = a[i][j];
-            }
-        const bool hasR = active && b < K - 1;
-        float c2[OWNC][C];
-#pragma unroll
-        for (int i = 0; i < OWNC; ++i) {
-            const int row = MC::row(lik, i);
-#pragma unroll
-            for (int j = 0; j < C; ++j)
-                c2[i][j] = (hasR && row >= 0) ? kn[L::oR + j * C + row] : (j == row ? 1.f : 0.f);
-        }
-        if (q.g_diag) {
-#pragma unroll
-            for (int i = 0; i < OWNC; ++i)
-#pragma unroll
-                for (int j = 0; j < C; ++j)
-                    if (MC::row(lik, i) == j) c2[i][j] = 1.0f / c2[i][j];
-        } else {
-            gj_invert_knot<MC, LPK>(c2, lik, lane);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < OWNC; ++i) {
-            const int row = MC::row(lik, i);
-            if (hasR && row >= 0) {
-#pragma unroll
-                for (int j = 0; j < C; ++j) kn[L::oR + j * C + row] = c2[i][j];
+                for (int i = 0; i < OWN; ++i) out[i][c] = fmaf(xv[i], y, out[i][c]);
             }
         }
-    }
-    __syncthreads();   // every stage's A, B, Q^-1, R^-1, q, r are in shared memory
-    stamp(p, 3);
+    };
 
-    // ==== 3. block row b in the own-row mapping: phi_b, gamma_b, theta_b, theta_b^-1 ==============
+    // ==== 2./3. two passes through ONE copy of the elimination code: pass 0 inverts Q_b (and R_b),
+    //      pass 1 forms block row b (phi_b, gamma_b, theta_b) and inverts theta_b.
     //   phi_b = A Q^-1, BR = B R^-1 (stage b-1), theta_b = phi A^T + Q_b^-1 + BR B^T,
     //   gamma_b = Q_b^-1 q_b - c_b + phi q_{b-1} + BR r_{b-1}          (src/gato_schur.cuh:277-385)
+    float a[OWN][S];       // rows being inverted; the shuffles need the whole warp, idle lanes carry an identity
+    float th[OWN][S];      // theta_b rows (kept for the S main block)
     float gam[OWN];
-    float thi[OWN][S];
-    {
-        float th[OWN][S];
 #pragma unroll
-        for (int i = 0; i < OWN; ++i) {
-            gam[i] = 0.f;
+    for (int i = 0; i < OWN; ++i) {
+        gam[i] = 0.f;
 #pragma unroll
-            for (int j = 0; j < S; ++j) th[i][j] = (MS::row(lik, i) == j) ? 1.f : 0.f;
-        }
-        if (active) {
+        for (int j = 0; j < S; ++j) th[i][j] = 0.f;
+    }
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll
+        for (int i = 0; i < OWN; ++i)
+#pragma unroll
+            for (int j = 0; j < S; ++j) a[i][j] = (!active && MS::row(lik, i) == j) ? 1.f : 0.f;
+        if (pass == 0) {
+            if (active && b == 0) {   // block row 0 keeps raw Q0 as theta_0^-1 (src/gato_schur.cuh:75-81): stash it
+#pragma unroll
+                for (int i = 0; i < OWN; ++i)
+                    if (ovr[i]) {
+#pragma unroll
+                        for (int ci = 0; ci < VS / 4; ++ci)
+                            reinterpret_cast<float4*>(kn + L::oPhi + orow[i] * VS)[ci] =
+                                reinterpret_cast<const float4*>(kn + L::oQ + orow[i] * VS)[ci];
+                    }
+            }
+            if (q.g_diag) {   // diagonal cost blocks: the inverses are reciprocals (same bits as the elimination)
+                if (active) {
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i)
+                        if (ovr[i]) {
+                            float* d = kn + L::oQ + orow[i] * VS + po0 + i;
+                            *d = 1.0f / *d;
+                        }
+                    if (b < K - 1) {
+#pragma unroll
+                        for (int i = 0; i < OWNC; ++i) {
+                            const int row = MC::row(lik, i);
+                            if (row >= 0) {
+                                float* d = kn + L::oR + row * LDC + row;
+                                *d = 1.0f / *d;
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+                stamp(p, 3);
+                continue;
+            }
+            if (active) {
+#pragma unroll
+                for (int i = 0; i < OWN; ++i)
+                    if (ovr[i]) load_row(kn + L::oQ + orow[i] * VS, a[i]);
+            }
+        } else if (active) {
             if (b == 0) {
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
-                    if (ov[i]) {
+                    if (ovr[i]) {
+                        float qv[S];
+                        load_row(kn + L::oQ + orow[i] * VS, a[i]);     // theta_0 = Q0^-1 (:26-149)
+                        load_row(kn + L::oq, qv);
                         float acc = 0.f;
 #pragma unroll
-                        for (int k = 0; k < S; ++k) {
-                            const float qi = kn[L::oQ + k * S + orow[i]];
-                            th[i][k] = qi;                               // theta_0 = Q0^-1 (:26-149)
-                            acc = fmaf(qi, kn[L::oq + k], acc);
-                        }
-                        gam[i] = acc;                                    // c[0:S] is ignored
+                        for (int k = 0; k < S; ++k) acc = fmaf(a[i][k], qv[k], acc);
+                        gam[i] = acc;                                  // c[0:S] is ignored
                     }
             } else {
                 const float* prev = kn - KN;
-                const float* Ap = prev + L::oA;
-                const float* Bp = prev + L::oB;
-                const float* Qip = prev + L::oQ;
-                const float* Rip = prev + L::oR;
+                float phi[OWN][S], br[OWN][C];
+#pragma unroll
+                for (int i = 0; i < OWN; ++i) {
+#pragma unroll
+                    for (int c = 0; c < S; ++c) phi[i][c] = 0.f;
+#pragma unroll
+                    for (int c = 0; c < C; ++c) br[i][c] = 0.f;
+                }
+                if (q.g_diag) {
+#pragma unroll
+                    for (int c = 0; c < S; ++c) {
+                        float xv[OWN];
+                        load_own(prev + L::oA + c * VS, xv);
+                        const float qi = prev[L::oQ + c * VS + L::pos(c)];
+#pragma unroll
+                        for (int i = 0; i < OWN; ++i) phi[i][c] = xv[i] * qi;
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        float xv[OWN];
+                        load_own(prev + L::oB + c * VS, xv);
+                        const float ri = prev[L::oR + c * LDC + c];
+#pragma unroll
+                        for (int i = 0; i < OWN; ++i) br[i][c] = xv[i] * ri;
+                    }
+                } else {
+                    rank1_S(phi, prev + L::oA, prev + L::oQ, S);
+                    rank1_C(br, prev + L::oB, prev + L::oR, C);
+                }
+#pragma unroll
+                for (int c = 0; c < S; ++c) {
+                    float col[OWN];
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i) col[i] = phi[i][c];
+                    store_own(kn + L::oPhi + c * VS, col);
+                }
+                {
+                    float qv[S], qp[S];
+                    load_row(kn + L::oq, qv);
+                    load_row(prev + L::oq, qp);
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i)
+                        if (ovr[i]) {
+                            float qrow[S];
+                            load_row(kn + L::oQ + orow[i] * VS, qrow);
+                            float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll
+                            for (int k = 0; k < S; ++k) {
+                                a0 = fmaf(qrow[k], qv[k], a0);
+                                a1 = fmaf(phi[i][k], qp[k], a1);
+                                a[i][k] = 0.f;
+                            }
+#pragma unroll
+                            for (int k = 0; k < C; ++k) a2 = fmaf(br[i][k], prev[L::or_ + k], a2);
+                            gam[i] = (a0 - __ldg(cv + b * S + orow[i])) + (a2 + a1);
+                        }
+                }
+                rank1_S(a, kn + L::oPhi, prev + L::oA, S);             // phi A^T
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
-                    if (ov[i]) {
-                        const int row = orow[i];
-                        float x[S], y[C], phi[S], br[C];
+                    if (ovr[i]) {
+                        float qrow[S];
+                        load_row(kn + L::oQ + orow[i] * VS, qrow);
 #pragma unroll
-                        for (int k = 0; k < S; ++k) x[k] = Ap[k * S + row];
-#pragma unroll
-                        for (int k = 0; k < C; ++k) y[k] = Bp[k * S + row];
-#pragma unroll
-                        for (int c0 = 0; c0 < S; ++c0) {
-                            float acc = 0.f;
-#pragma unroll
-                            for (int k = 0; k < S; ++k) acc = fmaf(x[k], Qip[c0 * S + k], acc);
-                            phi[c0] = acc;
-                            kn[L::oPhi + c0 * S + row] = acc;
-                        }
-#pragma unroll
-                        for (int c0 = 0; c0 < C; ++c0) {
-                            float acc = 0.f;
-#pragma unroll
-                            for (int k = 0; k < C; ++k) acc = fmaf(y[k], Rip[c0 * C + k], acc);
-                            br[c0] = acc;
-                        }
-                        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
-#pragma unroll
-                        for (int k = 0; k < S; ++k) {
-                            a0 = fmaf(kn[L::oQ + k * S + row], kn[L::oq + k], a0);
-                            a1 = fmaf(phi[k], prev[L::oq + k], a1);
-                        }
-#pragma unroll
-                        for (int k = 0; k < C; ++k) a2 = fmaf(br[k], prev[L::or_ + k], a2);
-                        gam[i] = (a0 - __ldg(cv + b * S + row)) + (a2 + a1);
-#pragma unroll
-                        for (int c0 = 0; c0 < S; ++c0) {
-                            float acc = 0.f;
-#pragma unroll
-                            for (int k = 0; k < S; ++k) acc = fmaf(phi[k], Ap[k * S + c0], acc);
-                            acc += kn[L::oQ + c0 * S + row];
-                            float acc2 = 0.f;
-#pragma unroll
-                            for (int k = 0; k < C; ++k) acc2 = fmaf(br[k], Bp[k * S + c0], acc2);
-                            th[i][c0] = acc + acc2;
-                        }
+                        for (int c = 0; c < S; ++c) a[i][c] += qrow[c];   // + Q_b^-1
                     }
+#pragma unroll
+                for (int k = 0; k < C; ++k) {                          // + BR B^T
+                    float yv[S];
+                    load_row(prev + L::oB + k * VS, yv);
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i)
+#pragma unroll
+                        for (int c = 0; c < S; ++c) a[i][c] = fmaf(br[i][k], yv[c], a[i][c]);
+                }
             }
-        }
-#pragma unroll
-        for (int i = 0; i < OWN; ++i)
-#pragma unroll
-            for (int j = 0; j < S; ++j) thi[i][j] = th[i][j];
-        // theta_b rows -> shared (tmp), to be re-read in the matrix mapping below
-        if (active && b > 0) {
-            // (block row 0's tmp still holds raw Q0; its theta_0 = Q0^-1 is re-read from the Q slot)
 #pragma unroll
             for (int i = 0; i < OWN; ++i)
-                if (ov[i]) {
 #pragma unroll
-                    for (int j = 0; j < S; ++j) kn[L::oTmp + j * S + orow[i]] = th[i][j];
+                for (int j = 0; j < S; ++j) th[i][j] = a[i][j];
+        }
+        gj_invert_knot<MS, LPK>(a, lik, lane);
+        if (pass == 0) {
+            if (active) {
+#pragma unroll
+                for (int i = 0; i < OWN; ++i)
+                    if (ovr[i]) store_row(kn + L::oQ + orow[i] * VS, a[i]);
+            }
+            const bool hasR = active && b < K - 1;
+            float c2[OWNC][C];
+#pragma unroll
+            for (int i = 0; i < OWNC; ++i) {
+                const int row = MC::row(lik, i);
+#pragma unroll
+                for (int j = 0; j < C; ++j)
+                    c2[i][j] = (hasR && row >= 0) ? kn[L::oR + row * LDC + j] : (!hasR && j == row ? 1.f : 0.f);
+            }
+            gj_invert_knot<MC, LPK>(c2, lik, lane);
+#pragma unroll
+            for (int i = 0; i < OWNC; ++i) {
+                const int row = MC::row(lik, i);
+                if (hasR && row >= 0) {
+#pragma unroll
+                    for (int j = 0; j < C; ++j) kn[L::oR + row * LDC + j] = c2[i][j];
                 }
+            }
+            __syncthreads();   // every stage's A, B, Q^-1, R^-1, q, r are in shared memory
+            stamp(p, 3);
         }
     }
-    gj_invert_knot<MS, LPK>(thi, lik, lane);             // warp-uniform; idle lanes invert an identity
+    // a = theta_b^-1 rows; block row 0 uses raw Q0 instead (the reference's Pinv[0] = Q0)
     if (active && b == 0) {
 #pragma unroll
         for (int i = 0; i < OWN; ++i)
-            if (ov[i]) {
-#pragma unroll
-                for (int j = 0; j < S; ++j) thi[i][j] = kn[L::oTmp + j * S + orow[i]];   // raw Q0
-            }
+            if (ovr[i]) load_row(kn + L::oPhi + orow[i] * VS, a[i]);
     }
     stamp(p, 4);
-    __syncthreads();   // phi_b of every block row (and theta_b in tmp) is in shared memory
+    __syncthreads();   // phi_b of every block row is in shared memory
 
     // ==== 4. iteration matrices into registers, matrix mapping ====================================
     // Lane (g, h) holds rows g*R .. g*R+R-1 of [S_left | S_main | S_right] restricted to its column
@@ -402,88 +509,93 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     // (H == 1): [left | main | right], VS positions each.  Pad positions are never touched.
     constexpr int NLOC = (H == 2) ? VS + HALFP : 3 * VS;
     constexpr int MAIN0 = VS;                      // first local column of the main block (both layouts)
-    constexpr int NMAIN = (H == 2) ? HALFP : VS;   // local columns of the main block held by a lane
     float Sm[R][NLOC], Tm[R][HALFP];
     {
-        const float* mainsrc = kn + (b == 0 ? L::oQ : L::oTmp);   // theta_0 = Q0^-1 sits in the Q slot
+        // own-row mapping (OWN rows x all columns) -> matrix mapping (R rows x own column half):
+        // the two lanes of a row group swap the quadrants they do not need
+        auto to_matrix = [&](const float (&own)[OWN][S], float (&mm)[R][HALFP]) {
 #pragma unroll
-        for (int i = 0; i < R; ++i) {
-            const int rr = g * R + i;
-            const bool rv = active && rr < S;
-            const int rs = rv ? rr : 0;
+            for (int i = 0; i < R; ++i)
 #pragma unroll
-            for (int l = 0; l < NMAIN; ++l) {
-                float v = 0.f;
-                if (l < HALFU) {
-                    const int col = h * HALFU + l;        // H == 1: h = 0, HALFU = S
-                    if (rv) v = mainsrc[col * S + rs];
-                }
-                Sm[i][MAIN0 + l] = v;
+                for (int l = 0; l < HALFP; ++l) mm[i][l] = 0.f;
+            if constexpr (H == 2) {
+#pragma unroll
+                for (int j = 0; j < OWN; ++j)
+#pragma unroll
+                    for (int l = 0; l < HALFU; ++l) {
+                        const float send = h ? own[j][l] : own[j][HALFU + l];
+                        const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                        mm[j][l] = h ? recv : own[j][l];                                   // rows [0, OWN)
+                        if (OWN + j < R) mm[OWN + j][l] = h ? own[j][HALFU + l] : recv;    // rows [OWN, R)
+                    }
+            } else {
+#pragma unroll
+                for (int j = 0; j < OWN; ++j)
+#pragma unroll
+                    for (int l = 0; l < S; ++l) mm[j][l] = own[j][l];
             }
+        };
+#pragma unroll
+        for (int i = 0; i < R; ++i)
+#pragma unroll
+            for (int l = 0; l < NLOC; ++l) Sm[i][l] = 0.f;
+        {
+            float mm[R][HALFP];
+            to_matrix(th, mm);
+#pragma unroll
+            for (int i = 0; i < R; ++i)
+#pragma unroll
+                for (int l = 0; l < HALFP; ++l) Sm[i][MAIN0 + l] = mm[i][l];
         }
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < OWN; ++i)
-            if (ov[i]) {
-#pragma unroll
-                for (int j = 0; j < S; ++j) kn[L::oTmp + j * S + orow[i]] = thi[i][j];
-            }
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < R; ++i) {
-            const int rr = g * R + i;
-            const bool rv = active && rr < S;
-            const int rs = rv ? rr : 0;
-#pragma unroll
-            for (int l = 0; l < HALFP; ++l) {
-                float v = 0.f;
-                if (l < HALFU) {
-                    const int col = h * HALFU + l;
-                    if (rv) v = kn[L::oTmp + col * S + rs];
-                }
-                Tm[i][l] = v;
-            }
-        }
+        to_matrix(a, Tm);
+
         const bool hasL = active && b > 0, hasR = active && b + 1 < K;
         const float* phiL = kn + L::oPhi;            // phi_b      : S[b,left]  = phi_b
         const float* phiR = kn + KN + L::oPhi;       // phi_{b+1}  : S[b,right] = phi_{b+1}^T
+        if constexpr (H == 2) {
+            if (h == 0) {
+                if (hasL) {   // phi_b[rr, c] at c*VS + pos(rr): the R rows of group g are contiguous
 #pragma unroll
-        for (int i = 0; i < R; ++i) {
-            const int rr = g * R + i;
-            const bool rv = active && rr < S;
-            const int rs = rv ? rr : 0;
-            if (H == 2) {
+                    for (int c = 0; c < S; ++c) {
 #pragma unroll
-                for (int l = 0; l < VS; ++l) {
-                    float v = 0.f;
-                    if (L::pos_valid(l)) {
-                        const int col = L::pos_row(l);
-                        if (h == 0) { if (rv && hasL) v = phiL[col * S + rs]; }
-                        else        { if (rv && hasR) v = phiR[rs * S + col]; }
+                        for (int ci = 0; ci < HALFP / 4; ++ci) {
+                            const float4 t = reinterpret_cast<const float4*>(phiL + c * VS + g * HALFP)[ci];
+                            const float e[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                if (4 * ci + u < R) Sm[4 * ci + u][L::pos(c)] = e[u];
+                        }
                     }
-                    Sm[i][l] = v;
                 }
-            } else {
+            } else if (hasR) {   // phi_{b+1}[c, rr] at rr*VS + pos(c): a whole row of S[b,right] is contiguous
 #pragma unroll
-                for (int l = 0; l < VS; ++l) {
-                    float vl = 0.f, vr = 0.f;
-                    if (l < S) {
-                        if (rv && hasL) vl = phiL[l * S + rs];
-                        if (rv && hasR) vr = phiR[rs * S + l];
+                for (int i = 0; i < R; ++i) {
+#pragma unroll
+                    for (int ci = 0; ci < VS / 4; ++ci) {
+                        const float4 t = reinterpret_cast<const float4*>(phiR + (g * R + i) * VS)[ci];
+                        const float e[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (L::pos_valid(4 * ci + u)) Sm[i][4 * ci + u] = e[u];
                     }
-                    Sm[i][l] = vl;
-                    Sm[i][2 * VS + l] = vr;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < R; ++i) {
+                const int rr = g * R + i;
+                const bool rv = rr < S;
+#pragma unroll
+                for (int l = 0; l < S; ++l) {
+                    if (rv && hasL) Sm[i][l] = phiL[l * VS + rr];
+                    if (rv && hasR) Sm[i][2 * VS + l] = phiR[rr * VS + l];
                 }
             }
         }
     }
     stamp(p, 5);
+
     // ---- iterate plumbing ------------------------------------------------------------------------
-    auto store_own = [&](float* xk, const float (&v)[OWN]) {   // xk = base of this knot's slot
-#pragma unroll
-        for (int j = 0; j < OWN; ++j)
-            if (ov[j]) xk[po[j]] = v[j];
-    };
     auto scatter = [&](const float (&acc)[R], float (&out)[OWN]) {   // combine the H column groups
         if (H == 2) {
 #pragma unroll
@@ -701,24 +813,31 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     }
     __syncthreads();
     if (active) {
-        const float* ln = xp + (b + 2) * VS;        // lambda_{b+1}; zero past the horizon
+        float ln[S];                                    // lambda_{b+1}; zero past the horizon
+        load_row(xp + (b + 2) * VS, ln);
+        float tb[OWN];
 #pragma unroll
         for (int j = 0; j < OWN; ++j) {
-            const int row = orow[j];
-            if (ov[j]) {
+            tb[j] = 0.f;
+            if (ovr[j]) {   // (A^T lambda_{b+1})[row] = sum_k A[k,row] lambda_{b+1}[k]: column `row` of A is contiguous
+                float col[S];
+                load_row(kn + L::oA + orow[j] * VS, col);
                 float acc = 0.f;
 #pragma unroll
-                for (int k = 0; k < S; ++k) acc = fmaf(kn[L::oA + row * S + k], ln[L::pos(k)], acc);
-                xz_k[po[j]] = kn[L::oq + row] - (lam[j] + acc);
+                for (int k = 0; k < S; ++k) acc = fmaf(col[k], ln[k], acc);
+                tb[j] = kn[L::oq + po0 + j] - (lam[j] + acc);
             }
         }
+        store_own(xz_k, tb);
 #pragma unroll
         for (int j = 0; j < OWNC; ++j) {
-            const int cr = MC::row(lik, j) < 0 ? C : MC::row(lik, j);
-            if (cr < C) {
+            const int cr = MC::row(lik, j);
+            if (cr >= 0) {
+                float col[S];
+                load_row(kn + L::oB + cr * VS, col);
                 float acc = 0.f;
 #pragma unroll
-                for (int k = 0; k < S; ++k) acc = fmaf(kn[L::oB + cr * S + k], ln[L::pos(k)], acc);
+                for (int k = 0; k < S; ++k) acc = fmaf(col[k], ln[k], acc);
                 xr_k[cr] = kn[L::or_ + cr] - acc;
             }
         }
@@ -726,24 +845,26 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     __syncwarp();
     if (active) {
         float* dz = p.dz_out + (long long)sys * p.lddz + (long long)b * (S + C);
+        float tbv[S];
+        load_row(xz_k, tbv);
 #pragma unroll
-        for (int j = 0; j < OWN; ++j) {
-            const int row = orow[j];
-            if (ov[j]) {
+        for (int j = 0; j < OWN; ++j)
+            if (ovr[j]) {
+                float qrow[S];
+                load_row(kn + L::oQ + orow[j] * VS, qrow);
                 float acc = 0.f;
 #pragma unroll
-                for (int k = 0; k < S; ++k) acc = fmaf(kn[L::oQ + k * S + row], xz_k[L::pos(k)], acc);
-                dz[row] = acc;
+                for (int k = 0; k < S; ++k) acc = fmaf(qrow[k], tbv[k], acc);
+                dz[orow[j]] = acc;
             }
-        }
         if (b < K - 1) {
 #pragma unroll
             for (int j = 0; j < OWNC; ++j) {
-                const int cr = MC::row(lik, j) < 0 ? C : MC::row(lik, j);
-                if (cr < C) {
+                const int cr = MC::row(lik, j);
+                if (cr >= 0) {
                     float acc = 0.f;
 #pragma unroll
-                    for (int k = 0; k < C; ++k) acc = fmaf(kn[L::oR + k * C + cr], xr_k[k], acc);
+                    for (int k = 0; k < C; ++k) acc = fmaf(kn[L::oR + cr * LDC + k], xr_k[k], acc);
                     dz[S + cr] = acc;
                 }
             }
