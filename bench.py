@@ -405,7 +405,8 @@ def ours_arm(args, rank, local_rank, world):
                     "outputs_match_resident_run": same},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "gato_fused_solve",
+                         "traffic": None, "peak_source": peak_src,
+                         "kernel": "gato_fused_solve_v2" if pl.kernel() == 2 else "gato_fused_solve",
                          "kernel_ms_avg": kavg_ms, "algorithmic_bytes_per_system": bps,
                          "fp32": {"achieved_tflops": tfl, "peak_tflops": FP32_PEAK_TFLOPS,
                                   "frac": tfl / FP32_PEAK_TFLOPS, "flops_per_launch": fl,

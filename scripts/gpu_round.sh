@@ -11,6 +11,6 @@ CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-single"
 $CMD > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:gato_fused -s 3 -c 1 -o gpurun_out/prof_fused $CMD > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:gato_fused_solve -s 3 -c 1 -o gpurun_out/prof_fused $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la gpurun_out
