@@ -90,6 +90,12 @@ struct gato_plan {
     PinBuf hin, hout;   // pinned staging for the single-solve path
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // chunk pipeline of the host-buffer batched path: H2D of chunk i+1 overlaps the kernel of chunk i
+    static constexpr int kPipe = 4;
+    int pipe_chunk = 0;     // systems per chunk; 0 = automatic, <0 = pipeline off
+    cudaStream_t pstream[kPipe] = {};
+    cudaEvent_t pev[kPipe] = {};
+    cudaEvent_t ev_shared = nullptr;
 };
 
 // ------------------------------------------------------------------------------------------------

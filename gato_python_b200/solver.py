@@ -19,7 +19,7 @@ WARM_OFF, WARM_REFERENCE, WARM_TRUE = 0, 1, 2
 #: every symbol include/gato_b200.h declares
 SYMBOLS = [
     "gato_supported_sizes", "gato_last_error", "gato_device_count", "gato_plan_create",
-    "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel",
+    "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel", "gato_plan_set_pipeline",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -53,6 +53,7 @@ def lib():
     L.gato_plan_set_cluster.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_get_cluster.argtypes = [C.c_void_p, _ip, _ip]
     L.gato_plan_set_kernel.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_set_pipeline.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
     L.gato_solve.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_int,
                              C.c_float, _ip, _fp]
@@ -139,6 +140,10 @@ class Plan:
 
     def kernel(self):
         return lib().gato_plan_get_kernel(self._h)
+
+    def set_pipeline(self, systems_per_chunk):
+        """Chunk size of the H2D / solve / D2H pipeline of solve_batched: 0 = automatic, < 0 = off."""
+        _check(lib().gato_plan_set_pipeline(self._h, int(systems_per_chunk)))
 
     def cluster(self):
         a, b = C.c_int(), C.c_int()

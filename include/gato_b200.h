@@ -64,6 +64,12 @@ int gato_plan_get_cluster(const gato_plan* plan, int* cluster_ctas, int* knots_p
 int gato_plan_set_kernel(gato_plan* plan, int kernel);
 int gato_plan_get_kernel(const gato_plan* plan);
 
+/* Chunk pipeline of gato_solve_batched: the batch is cut into chunks of `systems_per_chunk` systems
+ * whose H2D copy, kernel and D2H copy run on rotating streams, so the copy of chunk i+1 overlaps the
+ * solve of chunk i (the reference copies, solves and copies back strictly in sequence on stream 0,
+ * gpu_library.cu:150-157, 174, 71-72).  0 = automatic (default), < 0 = off (one chunk). */
+int gato_plan_set_pipeline(gato_plan* plan, int systems_per_chunk);
+
 /* One KKT solve, HOST buffers in and out.  Replaces main_call + gato_linsys
  * (gpu_library.cu:25-83, 85-231): H2D of values, one fused kernel, D2H of lambda and dz.
  * lambda_in may be NULL unless warm_start == GATO_WARM_TRUE.  iters_out (may be NULL) receives the

@@ -244,6 +244,29 @@ def test_batched_matches_single_and_oracle(kernel):
     pl.close()
 
 
+def test_batched_pipeline_is_bitwise_equal():
+    """The chunked H2D / solve / D2H pipeline of gato_solve_batched returns exactly what one chunk
+    returns: ragged last chunk, shared matrices, true warm start."""
+    n = 37
+    b = iiwa_like_batch(n, K=12, seed0=50)
+    pl = Plan(14, 7, 12, b["G_row"], b["G_col"], b["C_row"], b["C_col"])
+    args = (b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    pl.set_pipeline(-1)
+    ref = pl.solve_batched(*args)
+    for chunk in (5, 8, 36, 0):
+        pl.set_pipeline(chunk)
+        out = pl.solve_batched(*args)
+        assert all(np.array_equal(x, y) for x, y in zip(out[:3], ref[:3])), chunk
+    lam0 = (0.5 * ref[0]).astype(np.float32)
+    shared = (b["G_val"][0], b["C_val"][0], b["g"], b["c"], lam0, b["exit_tol"], b["max_iters"], WARM_TRUE, b["rho"])
+    pl.set_pipeline(-1)
+    ref = pl.solve_batched(*shared)
+    pl.set_pipeline(7)
+    out = pl.solve_batched(*shared)
+    assert all(np.array_equal(x, y) for x, y in zip(out[:3], ref[:3]))
+    pl.close()
+
+
 def test_full_size_batch_properties():
     """BASELINE.json configs[3] at full size (8192 systems): size-independent properties -- the KKT
     residual of every system in FP64, and equality with per-system solves on a sample."""
