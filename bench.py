@@ -60,6 +60,17 @@ def bytes_per_system(nnzG, nnzC):
     return 4 * (nnzG + nnzC + n_z + n_l) + 4 * (n_l + n_z)
 
 
+def ncu_traffic(kernel, nsys):
+    """dram bytes per launch of `kernel` from the committed ncu capture (profiles/ncu_traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        with open(p) as f:
+            e = json.load(f).get(kernel)
+        return int(e["bytes"]) if e and int(e["systems_per_launch"]) == nsys else None
+    except Exception:
+        return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -389,6 +400,7 @@ def ours_arm(args, rank, local_rank, world):
         tfl = fl / (kavg_ms * 1e-3) / 1e12
         h2d = 4 * nsys * (nnzG + nnzC + n_z + n_l)
         d2h = 4 * nsys * (n_l + n_z + 1)
+        kname = "gato_fused_solve_v2" if pl.kernel() == 2 else "gato_fused_solve"
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -405,8 +417,8 @@ def ours_arm(args, rank, local_rank, world):
                     "outputs_match_resident_run": same},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": None, "peak_source": peak_src,
-                         "kernel": "gato_fused_solve_v2" if pl.kernel() == 2 else "gato_fused_solve",
+                         "traffic": ncu_traffic(kname, nsys), "peak_source": peak_src,
+                         "kernel": kname, "algorithmic_bytes_per_launch": bps * nsys,
                          "kernel_ms_avg": kavg_ms, "algorithmic_bytes_per_system": bps,
                          "fp32": {"achieved_tflops": tfl, "peak_tflops": FP32_PEAK_TFLOPS,
                                   "frac": tfl / FP32_PEAK_TFLOPS, "flops_per_launch": fl,
