@@ -82,6 +82,8 @@ struct gato_plan {
     int g_diag = 0;         // G's pattern is purely diagonal
     int sm_count = 0;
     int smem_optin = 0;
+    int lam_slot = 0;       // gato_solve ping-pongs its output between two slots of dlo ...
+    bool have_lambda = false;   // ... so the previous lambda stays readable for GATO_WARM_RESIDENT
     // device: pattern maps
     int *d_gmap = nullptr, *d_cmap = nullptr, *d_gstart = nullptr, *d_cstart = nullptr;
     int *d_gdst2 = nullptr, *d_cdst2 = nullptr;   // v2: absolute shared-memory destinations

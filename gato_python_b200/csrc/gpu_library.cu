@@ -171,6 +171,79 @@ py::tuple linsys_solve_batched(iarr G_row, iarr G_col, farr G_val, iarr C_row, i
     return py::make_tuple(lam, dz, iters);
 }
 
+// EXT: block input, no CSR.  G_dense [nsys, (S^2+C^2)K-C^2] and C_dense
+// [nsys, (S^2+SC)(K-1)] are the reference's dense layouts (include/gato_defines.h:36-37); a leading
+// dimension of 1 shares the array between all systems.
+gato_plan* g_block_plan = nullptr;
+
+py::tuple linsys_solve_blocks(farr G_dense, farr C_dense, farr g_val, farr c_val, float exit_tol, int max_iters,
+                              float rho) {
+    constexpr int nG = (kS * kS + kC * kC) * kK - kC * kC, nC = (kS * kS + kS * kC) * (kK - 1);
+    if (G_dense.ndim() != 2 || C_dense.ndim() != 2 || g_val.ndim() != 2 || c_val.ndim() != 2)
+        throw py::value_error("G_dense, C_dense, g_val, c_val must be [nsys, n] arrays");
+    const int nsys = (int)g_val.shape(0);
+    if (G_dense.shape(1) != nG || C_dense.shape(1) != nC || g_val.shape(1) != kNz || c_val.shape(1) != kNl)
+        throw py::value_error("expected row lengths " + std::to_string(nG) + ", " + std::to_string(nC) + ", " +
+                              std::to_string(kNz) + ", " + std::to_string(kNl));
+    auto rows_ok = [&](const farr& a) { return a.shape(0) == nsys || a.shape(0) == 1; };
+    if (!rows_ok(G_dense) || !rows_ok(C_dense) || !rows_ok(c_val))
+        throw py::value_error("leading dimensions must be nsys or 1 (shared)");
+    if (!g_block_plan) {
+        int dev = 0;
+        if (const char* d = std::getenv("GATO_B200_DEVICE")) dev = std::atoi(d);
+        check(gato_plan_create_blocks(kS, kC, kK, dev, 1, &g_block_plan));
+    }
+    py::array_t<float> lam({nsys, kNl}), dz({nsys, kNz});
+    py::array_t<int> iters(nsys);
+    auto ld = [&](const farr& a) -> long long { return a.shape(0) == 1 && nsys > 1 ? 0 : (long long)a.shape(1); };
+    float ms = 0.f;
+    int rc;
+    {
+        py::gil_scoped_release nogil;
+        rc = gato_solve_batched(g_block_plan, nsys, G_dense.data(), ld(G_dense), C_dense.data(), ld(C_dense),
+                                g_val.data(), ld(g_val), c_val.data(), ld(c_val), nullptr, 0, lam.mutable_data(),
+                                dz.mutable_data(), iters.mutable_data(), exit_tol, max_iters, GATO_WARM_OFF, rho,
+                                &ms);
+    }
+    check(rc);
+    g_cache.avg_ms = g_cache.first_ms = ms;
+    return py::make_tuple(lam, dz, iters);
+}
+
+// EXT: MPC sequence.  g_val [T, n_z], c_val [T, n_l], rho [T]; G_val / C_val [T or 1, nnz].
+// warm_start=True chains lambda on the device (a TRUE warm start, r0 = gamma - S lambda_{t-1}); False
+// starts every step cold, which is also what the reference does with warm_start=True.
+py::tuple linsys_solve_sequence(iarr G_row, iarr G_col, farr G_val, iarr C_row, iarr C_col, farr C_val,
+                                farr g_val, farr c_val, farr rho, float exit_tol, int max_iters, bool warm_start) {
+    if (G_val.ndim() != 2 || C_val.ndim() != 2 || g_val.ndim() != 2 || c_val.ndim() != 2 || rho.ndim() != 1)
+        throw py::value_error("G_val, C_val, g_val, c_val must be [T, n] arrays and rho [T]");
+    const int T = (int)g_val.shape(0);
+    check_sizes(G_row.size(), G_col.size(), G_val.shape(1), C_row.size(), C_col.size(), C_val.shape(1),
+                g_val.shape(1), c_val.shape(1), kNl);
+    auto rows_ok = [&](const farr& a) { return a.shape(0) == T || a.shape(0) == 1; };
+    if (!rows_ok(G_val) || !rows_ok(C_val) || !rows_ok(c_val) || rho.shape(0) != T)
+        throw py::value_error("leading dimensions must be T or 1 (shared); rho must have T entries");
+    std::vector<int> gr(G_row.data(), G_row.data() + G_row.size()), gc(G_col.data(), G_col.data() + G_col.size());
+    std::vector<int> cr(C_row.data(), C_row.data() + C_row.size()), cc(C_col.data(), C_col.data() + C_col.size());
+    gato_plan* plan = plan_for(gr, gc, cr, cc);
+    py::array_t<float> lam({T, kNl}), dz({T, kNz});
+    py::array_t<int> iters(T);
+    auto ld = [&](const farr& a) -> long long { return a.shape(0) == 1 && T > 1 ? 0 : (long long)a.shape(1); };
+    float ms = 0.f;
+    int rc;
+    {
+        py::gil_scoped_release nogil;
+        rc = gato_solve_sequence(plan, T, G_val.data(), ld(G_val), C_val.data(), ld(C_val), g_val.data(),
+                                 ld(g_val), c_val.data(), ld(c_val), rho.data(), 0.f, nullptr,
+                                 lam.mutable_data(), dz.mutable_data(), iters.mutable_data(), exit_tol, max_iters,
+                                 warm_start ? GATO_WARM_TRUE : GATO_WARM_OFF, &ms);
+    }
+    check(rc);
+    g_cache.avg_ms = ms / (float)T;
+    g_cache.first_ms = ms;
+    return py::make_tuple(lam, dz, iters);
+}
+
 }  // namespace
 
 PYBIND11_MODULE(gpu_library, m) {
@@ -181,6 +254,8 @@ PYBIND11_MODULE(gpu_library, m) {
     m.def("linsys_solve", &linsys_solve);   // positional, like the reference (no py::arg names)
     m.def("linsys_solve_info", &linsys_solve_info);
     m.def("linsys_solve_batched", &linsys_solve_batched);
+    m.def("linsys_solve_blocks", &linsys_solve_blocks);
+    m.def("linsys_solve_sequence", &linsys_solve_sequence);
     m.def("set_true_warm_start", [](bool on) { g_cache.true_warm = on; });
     m.def("set_cluster", [](int cl) { if (g_cache.plan) check(gato_plan_set_cluster(g_cache.plan, cl)); });
 }

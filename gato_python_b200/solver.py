@@ -14,11 +14,12 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgato_b200.so")
 
-WARM_OFF, WARM_REFERENCE, WARM_TRUE = 0, 1, 2
+WARM_OFF, WARM_REFERENCE, WARM_TRUE, WARM_RESIDENT = 0, 1, 2, 3
 
 #: every symbol include/gato_b200.h declares
 SYMBOLS = [
     "gato_supported_sizes", "gato_last_error", "gato_device_count", "gato_plan_create",
+    "gato_plan_create_blocks", "gato_solve_sequence",
     "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel", "gato_plan_set_pipeline",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
@@ -48,6 +49,9 @@ def lib():
     L.gato_supported_sizes.argtypes = [_ip, C.c_int]
     L.gato_plan_create.argtypes = [C.c_int] * 3 + [_ip, _ip, C.c_int, _ip, _ip, C.c_int, C.c_int, C.c_int,
                                                   C.POINTER(C.c_void_p)]
+    L.gato_plan_create_blocks.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_void_p)]
+    L.gato_solve_sequence.argtypes = [C.c_void_p, C.c_int, _fp, _ll, _fp, _ll, _fp, _ll, _fp, _ll, _fp, C.c_float,
+                                      _fp, _fp, _fp, _ip, C.c_float, C.c_int, C.c_int, _fp]
     L.gato_plan_destroy.argtypes = [C.c_void_p]
     L.gato_plan_destroy.restype = None
     L.gato_plan_set_cluster.argtypes = [C.c_void_p, C.c_int]
@@ -104,13 +108,28 @@ def device_count():
 class Plan:
     """Sparsity pattern + persistent device workspace for one (S, C, K) on one GPU."""
 
-    def __init__(self, S, C_, K, G_row, G_col, C_row, C_col, device=0, max_batch=1):
+    def _sizes(self, S, C_, K, device):
         self.S, self.C, self.K = int(S), int(C_), int(K)
         self.n_z = (self.S + self.C) * self.K - self.C
         self.n_l = self.S * self.K
         self.g_dense = (self.S ** 2 + self.C ** 2) * self.K - self.C ** 2
         self.c_dense = (self.S ** 2 + self.S * self.C) * (self.K - 1)
         self.device = int(device)
+
+    @classmethod
+    def from_blocks(cls, S, C_, K, device=0, max_batch=1):
+        """Block-input plan (no CSR): G_val / C_val of every solve are the reference's dense layouts
+        (`pack_blocks`)."""
+        self = cls.__new__(cls)
+        self._sizes(S, C_, K, device)
+        self.nnzG, self.nnzC = self.g_dense, self.c_dense
+        h = C.c_void_p()
+        _check(lib().gato_plan_create_blocks(self.S, self.C, self.K, self.device, int(max_batch), C.byref(h)))
+        self._h = h
+        return self
+
+    def __init__(self, S, C_, K, G_row, G_col, C_row, C_col, device=0, max_batch=1):
+        self._sizes(S, C_, K, device)
         gr = np.ascontiguousarray(G_row, np.int32)
         gc = np.ascontiguousarray(G_col, np.int32)
         cr = np.ascontiguousarray(C_row, np.int32)
@@ -164,6 +183,47 @@ class Plan:
                                 _f(lam_in) if lam_in is not None else None, _f(lam), _f(dz),
                                 exit_tol, int(max_iters), int(warm_start), rho, C.byref(it), C.byref(ms)))
         return lam, dz, dict(iters=it.value, device_ms=ms.value)
+
+    # -- MPC sequence, host buffers ----------------------------------------------------------------
+    def solve_sequence(self, G_val, C_val, g, c, rho, lambda0=None, exit_tol=1e-6, max_iters=500,
+                       warm_start=WARM_TRUE):
+        """`nsteps` consecutive solves; arrays are [nsteps, n] or [n] (shared); `rho` a scalar or
+        [nsteps].  With WARM_TRUE step t starts from step t-1's lambda, which stays on the device.
+        -> (lambda [nsteps, S*K], dz [nsteps, n_z], iters [nsteps], device_ms)"""
+        g = np.ascontiguousarray(g, np.float32)
+        if g.ndim != 2 or g.shape[1] != self.n_z:
+            raise ValueError(f"g must be [nsteps, {self.n_z}]")
+        nsteps = g.shape[0]
+
+        def prep(a, n):
+            a = np.ascontiguousarray(a, np.float32)
+            if a.ndim == 1:
+                a = a[None]
+            if a.shape[1] != n or a.shape[0] not in (1, nsteps):
+                raise ValueError(f"expected [{nsteps} or 1, {n}], got {a.shape}")
+            return a, (0 if (a.shape[0] == 1 and nsteps > 1) else n)
+
+        G_val, ldG = prep(G_val, self.nnzG)
+        C_val, ldC = prep(C_val, self.nnzC)
+        c, ldc = prep(c, self.n_l)
+        rho = np.asarray(rho, np.float32)
+        if rho.ndim == 0:
+            rho_p, rho0 = None, float(rho)
+        else:
+            rho = np.ascontiguousarray(rho)
+            if rho.shape != (nsteps,):
+                raise ValueError(f"rho must be a scalar or [{nsteps}]")
+            rho_p, rho0 = _f(rho), 0.0
+        lam0 = _f32(lambda0, (self.n_l,)) if lambda0 is not None else None
+        lam = np.empty((nsteps, self.n_l), np.float32)
+        dz = np.empty((nsteps, self.n_z), np.float32)
+        iters = np.empty(nsteps, np.int32)
+        ms = C.c_float()
+        _check(lib().gato_solve_sequence(self._h, nsteps, _f(G_val), ldG, _f(C_val), ldC, _f(g), self.n_z, _f(c),
+                                         ldc, rho_p, rho0, _f(lam0) if lam0 is not None else None, _f(lam),
+                                         _f(dz), _i(iters), exit_tol, int(max_iters), int(warm_start),
+                                         C.byref(ms)))
+        return lam, dz, iters, ms.value
 
     # -- batch, host buffers ---------------------------------------------------------------------
     def solve_batched(self, G_val, C_val, g, c, lambda_in=None, exit_tol=1e-6, max_iters=500,
@@ -242,6 +302,25 @@ class Plan:
                                       int(max_iters), rho, C.byref(it), *ptrs,
                                       clk.ctypes.data_as(C.POINTER(C.c_longlong))))
         return dict(lam=lam, dz=dz, iters=it.value, S=S_, Pinv=P_, gamma=gam, Ginv=Gi, clk_ns=clk)
+
+
+def pack_blocks(Q, R, A, B):
+    """Per-knot blocks -> the reference's dense layouts, the value arrays of a
+    `Plan.from_blocks` plan.  Q [K,S,S], R [K-1,C,C]; A [K-1,S,S], B [K-1,S,C] are the blocks AS
+    STORED in C's block row k+1 (for x+ = Ax + Bu that is -A, -B).  Leading batch dimensions are
+    kept.  -> (G_dense [..., (S^2+C^2)K-C^2], C_dense [..., (S^2+SC)(K-1)])"""
+    Q, R, A, B = (np.asarray(x, np.float32) for x in (Q, R, A, B))
+    K, S = Q.shape[-3], Q.shape[-1]
+    Cc = R.shape[-1] if R.size else B.shape[-1]
+    lead = Q.shape[:-3]
+    cm = lambda x: np.swapaxes(x, -1, -2).reshape(x.shape[:-2] + (-1,))   # noqa: E731  column-major flatten
+    G = np.zeros(lead + (K, S * S + Cc * Cc), np.float32)
+    G[..., :, : S * S] = cm(Q)
+    if K > 1:
+        G[..., : K - 1, S * S:] = cm(R)
+    G = G.reshape(lead + (-1,))[..., : (S * S + Cc * Cc) * K - Cc * Cc]
+    Cd = np.concatenate([cm(A), cm(B)], axis=-1).reshape(lead + (-1,)) if K > 1 else np.zeros(lead + (0,), np.float32)
+    return np.ascontiguousarray(G), np.ascontiguousarray(Cd)
 
 
 # ------------------------------------------------------------------------------------------------

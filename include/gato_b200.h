@@ -29,6 +29,10 @@ extern "C" {
                                   accepted and has NO numerical effect (src/gato_pcg.cuh:300-304) */
 #define GATO_WARM_TRUE 2       /* extension: r0 = gamma - S*lambda_in                            */
 
+#define GATO_WARM_RESIDENT 3   /* extension, gato_solve only: GATO_WARM_TRUE with lambda_in = the lambda
+                                  this plan's previous gato_solve left on the device (nothing is
+                                  uploaded; the first solve of a plan starts cold)                 */
+
 typedef struct gato_plan gato_plan; /* opaque: sparsity pattern maps + persistent device workspace */
 
 /* Which (STATE_SIZE, CONTROL_SIZE) pairs this build of the library carries kernels for.
@@ -50,6 +54,17 @@ int gato_plan_create(int S, int C, int K,
                      const int* G_row, const int* G_col, int nnzG,
                      const int* C_row, const int* C_col, int nnzC,
                      int device, int max_batch, gato_plan** plan_out);
+
+/* Block-input plan: no CSR at all.  The `G_val` / `C_val` arguments of every solve entry point are
+ * then the reference's own dense device layouts (include/gato_defines.h:36-37):
+ *   G_val = G dense, (S^2+C^2)K - C^2 floats: knot k at k(S^2+C^2): Q_k col-major, then R_k col-major
+ *   C_val = C dense, (S^2+SC)(K-1) floats:    stage k at k(S^2+SC): A_k col-major, then B_k col-major,
+ *           A_k / B_k as stored in C's block row k+1 (sign included, i.e. -A, -B for x+ = Ax + Bu)
+ * i.e. what gato_convert_kkt_format (src/gato_schur.cuh:745-756) would have produced (rho is still
+ * added to the Q/R diagonals by the solve).  Replaces the caller-side dense -> CSR conversion of
+ * test_IIWA50.py:11-18 plus the CSR -> dense kernel.  Results equal those of a CSR plan over the
+ * fully dense pattern. */
+int gato_plan_create_blocks(int S, int C, int K, int device, int max_batch, gato_plan** plan_out);
 void gato_plan_destroy(gato_plan* plan);
 
 /* Cluster shape override for tuning: `cluster_ctas` CTAs per system (0 = automatic). */
@@ -94,6 +109,21 @@ int gato_solve_batched(gato_plan* plan, int nsys,
                        float* lambda_out, float* dz_out, int* iters_out,
                        float exit_tol, int max_iters, int warm_start, float rho,
                        float* device_ms_out);
+
+/* MPC sequence (BASELINE.json config 5): `nsteps` CONSECUTIVE solves over the plan's pattern, HOST
+ * buffers; step t uses row t of each input array (ld == 0: shared by all steps) and rho[t] (rho ==
+ * NULL: rho0 for every step).  With warm_start == GATO_WARM_TRUE step t starts from the lambda of
+ * step t-1, which never leaves the device (step 0 from lambda0, or cold if lambda0 == NULL); with
+ * GATO_WARM_OFF / GATO_WARM_REFERENCE every step starts cold like the reference
+ * (src/gato_pcg.cuh:300-304).  One H2D of all inputs, nsteps back-to-back launches on one stream,
+ * one D2H of lambda_out [nsteps][S*K], dz_out [nsteps][(S+C)K-C], iters_out [nsteps].  Replaces a
+ * host loop over linsys_solve (gpu_library.cu:85-231) that re-uploads and re-allocates every step. */
+int gato_solve_sequence(gato_plan* plan, int nsteps,
+                        const float* G_val, long long ldG, const float* C_val, long long ldC,
+                        const float* g, long long ldg, const float* c, long long ldc,
+                        const float* rho, float rho0, const float* lambda0,
+                        float* lambda_out, float* dz_out, int* iters_out,
+                        float exit_tol, int max_iters, int warm_start, float* device_ms_out);
 
 /* Same, DEVICE buffers on the plan's device, asynchronous on `stream` (a cudaStream_t passed as
  * void*; NULL = legacy default stream, which is what the reference uses, include/gato_defines.h:22).

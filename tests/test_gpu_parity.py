@@ -324,3 +324,168 @@ def test_python_mirror_and_smoke():
     assert np.allclose(np.concatenate([dz, l]), np.concatenate([dz64, lam64]), rtol=1, atol=0.01)
     import __graft_entry__
     __graft_entry__.smoke()
+
+
+# ---- block-input plan, device-resident warm start, MPC sequence ---------------------
+def _dense_layouts(prob):
+    """The reference's dense layouts of a problem's G and C (rho NOT added), via the oracle's unpack."""
+    S, C, K = prob["S"], prob["C"], prob["K"]
+    return orc.unpack_kkt(S, C, K, prob["G_row"], prob["G_col"], prob["G_val"], prob["C_row"], prob["C_col"],
+                          prob["C_val"], 0.0)
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+@pytest.mark.parametrize("name", ["pendulum5", "iiwa50_s0", "iiwa50_dense", "ragged_K1", "odd_S7_K33"])
+def test_block_input_plan(name, kernel):
+    """gato_plan_create_blocks: value arrays = the reference's dense layouts.  Must match the oracle
+    like the CSR path, and equal the CSR path bit for bit when the CSR pattern is fully dense."""
+    prob = CASES[name]()
+    S, C, K = prob["S"], prob["C"], prob["K"]
+    Gd, Cd = _dense_layouts(prob)
+    pb = Plan.from_blocks(S, C, K)
+    pb.set_kernel(kernel)
+    assert (pb.nnzG, pb.nnzC) == (Gd.size, Cd.size)
+    lam, dz, info = pb.solve(Gd, Cd, prob["g"], prob["c"], None, prob["exit_tol"], prob["max_iters"], 0, prob["rho"])
+    lam_o, dz_o, io = oracle(prob)
+    assert close(lam, lam_o) and close(dz, dz_o) and abs(info["iters"] - io["iters"]) <= 1
+    # unpack hook of a block plan is the identity + rho on the diagonals
+    Gu, Cu = pb.unpack(Gd, Cd, prob["rho"])
+    Go, Co = orc.unpack_kkt(S, C, K, prob["G_row"], prob["G_col"], prob["G_val"], prob["C_row"], prob["C_col"],
+                            prob["C_val"], prob["rho"])
+    assert np.array_equal(Gu, Go) and np.array_equal(Cu, Co)
+    if name == "iiwa50_dense":
+        pc = plan_of(prob)
+        pc.set_kernel(kernel)
+        lam_c, dz_c, info_c = gpu(pc, prob)
+        assert info_c["iters"] == info["iters"] and close(lam, lam_c, 1e-5) and close(dz, dz_c, 1e-5)
+        pc.close()
+    pb.close()
+
+
+def test_block_input_batched():
+    nsys = 64
+    b = iiwa_like_batch(nsys, K=12, seed0=300)
+    base = dict(b, G_val=b["G_val"][0], C_val=b["C_val"][0], g=b["g"][0], c=b["c"][0])
+    lay = [_dense_layouts(dict(base, G_val=b["G_val"][i], C_val=b["C_val"][i])) for i in range(nsys)]
+    Gd = np.stack([x[0] for x in lay]); Cd = np.stack([x[1] for x in lay])
+    pb = Plan.from_blocks(b["S"], b["C"], b["K"], max_batch=nsys)
+    lam, dz, iters, _ = pb.solve_batched(Gd, Cd, b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    pc = Plan(b["S"], b["C"], b["K"], b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=nsys)
+    lam_c, dz_c, it_c, _ = pc.solve_batched(b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"],
+                                            b["max_iters"], 0, b["rho"])
+    assert np.abs(iters - it_c).max() <= 1
+    for i in range(nsys):
+        assert close(lam[i], lam_c[i]) and close(dz[i], dz_c[i]), i
+    pb.close(); pc.close()
+
+
+def _mpc_inputs(prob, nsteps, seed=0):
+    rng = np.random.default_rng(seed)
+    g = np.empty((nsteps, prob["g"].size), np.float32); c = np.empty((nsteps, prob["c"].size), np.float32)
+    gi, ci = prob["g"].copy(), prob["c"].copy()
+    for t in range(nsteps):
+        gi = (gi * (1 + 0.01 * rng.standard_normal(gi.size))).astype(np.float32)
+        ci = (ci * (1 + 0.01 * rng.standard_normal(ci.size))).astype(np.float32)
+        g[t], c[t] = gi, ci
+    rho = np.logspace(-4, -1, nsteps).astype(np.float32)
+    return g, c, rho
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+def test_sequence_api_matches_step_by_step(kernel):
+    """gato_solve_sequence == the same solves issued one by one (bitwise), in the reference-faithful
+    mode and with the true warm start; the warm chain equals GATO_WARM_RESIDENT and the oracle."""
+    from gato_python_b200.solver import WARM_RESIDENT
+    prob = iiwa_like(K=50, seed=9)
+    nsteps = 6
+    g, c, rho = _mpc_inputs(prob, nsteps)
+    pl = plan_of(prob)
+    pl.set_kernel(kernel)
+    # reference-faithful: every step cold
+    lam, dz, iters, _ = pl.solve_sequence(prob["G_val"], prob["C_val"], g, c, rho, None, prob["exit_tol"],
+                                          prob["max_iters"], WARM_REFERENCE)
+    for t in range(nsteps):
+        l1, d1, i1 = gpu(pl, dict(prob, g=g[t], c=c[t], rho=float(rho[t])))
+        assert np.array_equal(l1, lam[t]) and np.array_equal(d1, dz[t]) and i1["iters"] == iters[t]
+    # true warm start chained on the device
+    lam_w, dz_w, it_w, _ = pl.solve_sequence(prob["G_val"], prob["C_val"], g, c, rho, None, prob["exit_tol"],
+                                             prob["max_iters"], WARM_TRUE)
+    assert np.array_equal(lam_w[0], lam[0])          # step 0 has nothing to start from
+    assert it_w[1:].mean() < iters[1:].mean()        # the warm start pays
+    prev = None
+    for t in range(nsteps):
+        p = dict(prob, g=g[t], c=c[t], rho=float(rho[t]))
+        l1, d1, i1 = pl.solve(prob["G_val"], prob["C_val"], g[t], c[t], None, prob["exit_tol"], prob["max_iters"],
+                              WARM_RESIDENT, float(rho[t]))
+        assert np.array_equal(l1, lam_w[t]) and np.array_equal(d1, dz_w[t]) and i1["iters"] == it_w[t], t
+        if prev is not None:
+            lam_o, dz_o, io = oracle(p, lambda0=prev, warm=True, true_warm_start=True)
+            assert close(lam_w[t], lam_o) and close(dz_w[t], dz_o) and abs(int(it_w[t]) - io["iters"]) <= 1, t
+        prev = lam_w[t]
+    # lambda0 given: step 0 warm too
+    lam_x, _, it_x, _ = pl.solve_sequence(prob["G_val"], prob["C_val"], g[:1], c[:1], rho[:1], lam[0],
+                                          prob["exit_tol"], prob["max_iters"], WARM_TRUE)
+    assert it_x[0] <= 2 and close(lam_x[0], lam[0])
+    pl.close()
+
+
+def test_warm_resident_is_dropped_by_other_entry_points():
+    from gato_python_b200.solver import WARM_RESIDENT
+    prob = iiwa_like(K=12, seed=3)
+    pl = plan_of(prob)
+    l0, _, i0 = gpu(pl, prob)
+    l1, _, i1 = gpu(pl, prob, warm=WARM_RESIDENT)
+    assert i1["iters"] <= 1 and close(l1, l0)
+    pl.solve_batched(prob["G_val"], prob["C_val"], prob["g"][None], prob["c"], None, prob["exit_tol"],
+                     prob["max_iters"], 0, prob["rho"])            # reuses the output buffer
+    l2, _, i2 = gpu(pl, prob, warm=WARM_RESIDENT)                   # -> cold again, not garbage
+    assert i2["iters"] == i0["iters"] and np.array_equal(l2, l0)
+    pl.close()
+
+
+_DROPIN_EXT_CHILD = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[2])
+import gpu_library as g
+from gato_python_b200.problems import iiwa_like
+from gato_python_b200.solver import pack_blocks
+d = np.load(sys.argv[3])
+p = iiwa_like(K=50, seed=9)
+T = d["g"].shape[0]
+lam, dz, it = g.linsys_solve_sequence(p["G_row"], p["G_col"], p["G_val"][None], p["C_row"], p["C_col"], p["C_val"][None],
+                                      d["g"], d["c"], d["rho"], 1e-6, 500, True)
+lam0, dz0, it0 = g.linsys_solve_sequence(p["G_row"], p["G_col"], p["G_val"][None], p["C_row"], p["C_col"],
+                                         p["C_val"][None], d["g"], d["c"], d["rho"], 1e-6, 500, False)
+lb, dzb, itb = g.linsys_solve_blocks(d["Gd"][None], d["Cd"][None], d["g"], d["c"][:1], 1e-6, 500, 1e-3)
+np.savez(sys.argv[4], lam=lam, dz=dz, it=it, lam0=lam0, it0=it0, lb=lb, dzb=dzb, itb=itb)
+"""
+
+
+def test_dropin_module_extensions():
+    """gpu_library.linsys_solve_sequence / linsys_solve_blocks of the drop-in module (NumPy in and out)."""
+    import subprocess
+    import tempfile
+    md = refrun.dropin_module_dir(14, 7, 50)
+    if md is None:
+        pytest.skip("drop-in module not built")
+    prob = iiwa_like(K=50, seed=9)
+    T = 4
+    g, c, rho = _mpc_inputs(prob, T)
+    Gd, Cd = _dense_layouts(prob)
+    root = os.path.join(os.path.dirname(__file__), "..")
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.npz"), os.path.join(td, "out.npz")
+        np.savez(fin, g=g, c=c, rho=rho, Gd=Gd, Cd=Cd)
+        r = subprocess.run([sys.executable, "-c", _DROPIN_EXT_CHILD, md, root, fin, fout], capture_output=True,
+                           text=True, timeout=300)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        o = np.load(fout)
+    pl = plan_of(prob)
+    lam_w, dz_w, it_w, _ = pl.solve_sequence(prob["G_val"], prob["C_val"], g, c, rho, None, 1e-6, 500, WARM_TRUE)
+    lam_c, _, it_c, _ = pl.solve_sequence(prob["G_val"], prob["C_val"], g, c, rho, None, 1e-6, 500, 0)
+    assert np.array_equal(o["lam"], lam_w) and np.array_equal(o["dz"], dz_w) and np.array_equal(o["it"], it_w)
+    assert np.array_equal(o["lam0"], lam_c) and np.array_equal(o["it0"], it_c)
+    pl.close()
+    for t in range(T):   # blocks: c shared (row 0), rho fixed
+        lam_o, dz_o, io = oracle(dict(prob, g=g[t], c=c[0], rho=1e-3))
+        assert close(o["lb"][t], lam_o) and close(o["dzb"][t], dz_o) and abs(int(o["itb"][t]) - io["iters"]) <= 1
