@@ -262,13 +262,13 @@ def reference_arm(args, rank):
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
-def single_solve_latency(torch, Plan, dev_index, reps=300):
+def single_solve_latency(torch, Plan, dev_index, reps=300, knots=K):
     """IIWA-50 single solve: kernel-only (CUDA events around the launch, inputs resident) and the
     reference's bracket (H2D + kernel + D2H, gpu_library.cu:172-187) through gato_solve."""
     from gato_python_b200.problems import iiwa_like
 
-    prob = iiwa_like(S, C, K, seed=0)
-    pl = Plan(S, C, K, prob["G_row"], prob["G_col"], prob["C_row"], prob["C_col"], device=dev_index)
+    prob = iiwa_like(S, C, knots, seed=0)
+    pl = Plan(S, C, knots, prob["G_row"], prob["G_col"], prob["C_row"], prob["C_col"], device=dev_index)
     dev = torch.device("cuda", dev_index)
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(dev)   # noqa: E731
     G, Cv, g, c = t(prob["G_val"]), t(prob["C_val"]), t(prob["g"]), t(prob["c"])
@@ -293,10 +293,53 @@ def single_solve_latency(torch, Plan, dev_index, reps=300):
         _, _, info = pl.solve(prob["G_val"], prob["C_val"], prob["g"], prob["c"], None, prob["exit_tol"],
                               prob["max_iters"], 0, prob["rho"])
         bs.append(info["device_ms"] * 1e3)
-    out = {"workload": "iiwa50_single_solve_seed0", "iters": int(it.item()),
+    out = {"workload": f"iiwa{knots}_single_solve_seed0", "kernel": pl.kernel(), "iters": int(it.item()),
            "kernel_us_median": float(np.median(ks)), "kernel_us_min": float(np.min(ks)),
            "bracket_us_median": float(np.median(bs)), "bracket_us_p99": float(np.percentile(bs, 99)),
            "cluster": list(pl.cluster()), "reps": reps}
+    pl.close()
+    return out
+
+
+def mpc_sequence(Plan, dev_index, nsteps=1000):
+    """BASELINE.json config 5: `nsteps` CONSECUTIVE IIWA-50 solves (g, c follow a 1 % random walk, rho swept
+    1e-4 .. 1e-1), host buffers in and out.  `cold` = what the reference computes with warm_start=True
+    (the flag has no numerical effect there, src/gato_pcg.cuh:300-304); `warm` = the opt-in true warm start
+    with lambda chained on the device (gato_solve_sequence); `closed_loop` = one gato_solve per step with
+    GATO_WARM_RESIDENT, the form a controller that computes step t+1's g, c from step t's dz would use."""
+    from gato_python_b200.problems import iiwa_like
+    from gato_python_b200.solver import WARM_REFERENCE, WARM_RESIDENT, WARM_TRUE
+
+    prob = iiwa_like(S, C, K, seed=9)
+    rng = np.random.default_rng(0)
+    g = np.empty((nsteps, prob["g"].size), np.float32); c = np.empty((nsteps, prob["c"].size), np.float32)
+    gi, ci = prob["g"].copy(), prob["c"].copy()
+    for t in range(nsteps):
+        gi = (gi * (1 + 0.01 * rng.standard_normal(gi.size))).astype(np.float32)
+        ci = (ci * (1 + 0.01 * rng.standard_normal(ci.size))).astype(np.float32)
+        g[t], c[t] = gi, ci
+    rho = np.logspace(-4, -1, nsteps).astype(np.float32)
+    pl = Plan(S, C, K, prob["G_row"], prob["G_col"], prob["C_row"], prob["C_col"], device=dev_index)
+    out = {"workload": f"iiwa50_mpc_{nsteps}_consecutive_solves_rho_1e-4_to_1e-1", "steps": nsteps}
+    for name, mode in (("cold", WARM_REFERENCE), ("warm", WARM_TRUE)):
+        pl.solve_sequence(prob["G_val"], prob["C_val"], g[:50], c[:50], rho[:50], None, prob["exit_tol"],
+                          prob["max_iters"], mode)
+        t0 = time.perf_counter()
+        _, _, its, ms = pl.solve_sequence(prob["G_val"], prob["C_val"], g, c, rho, None, prob["exit_tol"],
+                                          prob["max_iters"], mode)
+        wall = time.perf_counter() - t0
+        out[name] = {"solves_per_s": nsteps / wall, "us_per_solve_wall": wall / nsteps * 1e6,
+                     "us_per_solve_device": ms * 1e3 / nsteps, "mean_iters": float(its.mean()),
+                     "max_iters": int(its.max())}
+    t0 = time.perf_counter()
+    its = []
+    for t in range(nsteps):
+        _, _, info = pl.solve(prob["G_val"], prob["C_val"], g[t], c[t], None, prob["exit_tol"], prob["max_iters"],
+                              WARM_RESIDENT, float(rho[t]))
+        its.append(info["iters"])
+    wall = time.perf_counter() - t0
+    out["closed_loop_warm_resident"] = {"solves_per_s": nsteps / wall, "us_per_solve_wall": wall / nsteps * 1e6,
+                                        "mean_iters": float(np.mean(its))}
     pl.close()
     return out
 
@@ -430,6 +473,8 @@ def ours_arm(args, rank, local_rank, world):
         }
         if world == 1 and not args.no_single:
             line["single_solve"] = single_solve_latency(torch, Plan, local_rank)
+            line["single_solve_k256"] = single_solve_latency(torch, Plan, local_rank, reps=100, knots=256)
+            line["mpc_sequence"] = mpc_sequence(Plan, local_rank)
         print(json.dumps(line), flush=True)
     pl.close()
     if world > 1:

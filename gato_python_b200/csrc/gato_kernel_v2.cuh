@@ -148,6 +148,15 @@ __device__ __forceinline__ void gj_invert_knot(float (&a)[M::N][M::D], int lik, 
     }
 }
 
+// eta / v without the IEEE division subroutine: reciprocal seed + one residual correction (the
+// quotient is correctly rounded except in rare last-bit cases; operands are far from the range ends)
+__device__ __forceinline__ float fast_div(float a, float b) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+    const float qv = a * r;
+    return fmaf(fmaf(-b, qv, a), r, qv);
+}
+
 struct SolveParams2 {
     SolveParams p;        // same arguments as the cluster kernel; gmap/cmap are unused here
     const int* gdst;      // [nnzG] absolute shared-memory float offset of each G non-zero (bit30 = diagonal)
@@ -237,24 +246,48 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     const float* cv = p.c + (long long)sys * p.ldc;
 
     // ==== 1. unpack: coalesced reads of the CSR values, scatter into the dense per-knot blocks ====
-#pragma unroll 4
-    for (int t = tid; t < q.nnzC; t += NT) {
-        const int m = __ldg(q.cdst + t);
-        const float v = __ldg(Cv + t);
-        if (m >= 0) smem[m] = v;
-    }
-#pragma unroll 4
-    for (int t = tid; t < q.nnzG; t += NT) {
-        const int m = __ldg(q.gdst + t);
-        const float v = __ldg(Gv + t);
-        smem[m & kMapMask] = v + ((m & kMapDiagBit) ? p.rho : 0.0f);
-    }
-    {   // g -> per-knot q (pos layout) | r
+    // One CTA per SM means HBM latency is hidden only by the loads each thread keeps in flight: every
+    // round issues UB (map, value) pairs per thread before the first dependent store.
+    {
+        constexpr int UB = 16;
+#pragma unroll 1
+        for (int t0 = tid; t0 < q.nnzC; t0 += NT * UB) {
+            int m[UB];
+            float v[UB];
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const int t = t0 + u * NT;
+                m[u] = -1;
+                v[u] = 0.f;
+                if (t < q.nnzC) { m[u] = __ldg(q.cdst + t); v[u] = __ldg(Cv + t); }
+            }
+#pragma unroll
+            for (int u = 0; u < UB; ++u)
+                if (m[u] >= 0) smem[m[u]] = v[u];
+        }
+        constexpr int UG = 8;
         const int n_z = (S + C) * K - C;
-#pragma unroll 4
-        for (int t = tid; t < n_z; t += NT) {
-            const int k = t / (S + C), o = t - k * (S + C);
-            smem[k * KN + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = __ldg(gv + t);
+#pragma unroll 1
+        for (int t0 = tid; t0 < max(q.nnzG, n_z); t0 += NT * UG) {
+            int m[UG];
+            float v[UG], w[UG];
+#pragma unroll
+            for (int u = 0; u < UG; ++u) {
+                const int t = t0 + u * NT;
+                m[u] = -1;
+                v[u] = w[u] = 0.f;
+                if (t < q.nnzG) { m[u] = __ldg(q.gdst + t); v[u] = __ldg(Gv + t); }
+                if (t < n_z) w[u] = __ldg(gv + t);
+            }
+#pragma unroll
+            for (int u = 0; u < UG; ++u) {
+                const int t = t0 + u * NT;
+                if (m[u] >= 0) smem[m[u] & kMapMask] = v[u] + ((m[u] & kMapDiagBit) ? p.rho : 0.0f);
+                if (t < n_z) {   // g -> per-knot q (pos layout) | r
+                    const int k = t / (S + C), o = t - k * (S + C);
+                    smem[k * KN + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = w[u];
+                }
+            }
         }
     }
     __syncthreads();
@@ -777,7 +810,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         }
         __syncthreads();
         const float v = block_partials_sum(redA, NW4);
-        const float alpha = eta / v;
+        const float alpha = fast_div(eta, v);
 #pragma unroll
         for (int j = 0; j < OWN; ++j) {
             lam[j] = fmaf(alpha, pp[j], lam[j]);
@@ -795,7 +828,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         const float eta_new = block_partials_sum(redB, NW4);
         eta_last = eta_new;
         if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
-        const float beta = eta_new / eta;
+        const float beta = fast_div(eta_new, eta);
 #pragma unroll
         for (int j = 0; j < OWN; ++j) pp[j] = fmaf(beta, pp[j], rt[j]);
         store_own(xp_k, pp);
