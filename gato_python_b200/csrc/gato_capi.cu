@@ -82,6 +82,7 @@ struct gato_plan {
     int g_diag = 0;         // G's pattern is purely diagonal
     int sm_count = 0;
     int smem_optin = 0;
+    int staging = 1;        // v2: TMA staging of the value arrays when it fits (gato_plan_set_staging)
     int lam_slot = 0;       // gato_solve ping-pongs its output between two slots of dlo ...
     bool have_lambda = false;   // ... so the previous lambda stays readable for GATO_WARM_RESIDENT
     // device: pattern maps
@@ -186,18 +187,38 @@ int v2_pick_nt(const gato_plan* pl) {   // smallest menu entry that holds K knot
     using L = gato::Layout2<S, C>;
     for (int i = 0; i < V2Menu<S>::n; ++i) {
         const int nt = V2Menu<S>::nt[i];
-        if (nt >= L::LPK * pl->K && (size_t)L::smem_floats(pl->K, nt) * 4 <= (size_t)pl->smem_optin) return nt;
+        if (nt >= L::LPK * pl->K && (size_t)(L::smem_floats(pl->K, nt) + 8) * 4 <= (size_t)pl->smem_optin) return nt;
     }
     return 0;
 }
 
 template <int S, int C, int NT>
-int launch_v2_t(const gato::SolveParams2& q, cudaStream_t st) {
+int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     using L = gato::Layout2<S, C>;
     auto kern = gato::gato_fused_solve_v2<S, C, NT>;
-    const size_t smem = (size_t)L::smem_floats(q.p.K, NT) * 4;
-    GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)q.p.nsys, NT, smem, st>>>(q);
+    const int core = L::smem_floats(q.p.K, NT);
+    // TMA staging of the C / G / g values (+ 16 bytes for the mbarrier) when it fits beside the system
+    const int stage = gato::stage_len(q.nnzC) + gato::stage_len(q.nnzG) + gato::stage_len(pl->n_z);
+    const int tail = 8;   // mbarrier + loop state of the persistent CTA
+    const bool staged = pl->staging && (size_t)(core + stage + tail) * 4 <= (size_t)pl->smem_optin;
+    q.stage_off = staged ? core : 0;
+    q.tail_off = core + (staged ? stage : 0);
+    const size_t smem = (size_t)(q.tail_off + tail) * 4;
+    // persistent grid: as many CTAs as are resident at once, each walking systems i, i + grid, ...
+    constexpr int kMaxDev = 64;   // the attribute is per device: cache (smem -> occupancy) per device
+    static int occ_smem[kMaxDev], occ_val[kMaxDev];
+    const int di = pl->device % kMaxDev;
+    if (occ_smem[di] != (int)smem) {
+        int occ = 0;
+        GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+        if (occ < 1) return fail(GATO_EUNSUPPORTED, "one-CTA kernel does not fit an SM (%zu B shared memory)", smem);
+        occ_smem[di] = (int)smem;
+        occ_val[di] = occ;
+    }
+    const int resident = occ_val[di] * (pl->sm_count > 0 ? pl->sm_count : 148);
+    const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
+    kern<<<grid, NT, smem, st>>>(q);
     GATO_CUDA(cudaGetLastError());
     return GATO_OK;
 }
@@ -205,10 +226,10 @@ int launch_v2_t(const gato::SolveParams2& q, cudaStream_t st) {
 template <int S, int C>
 int launch_v2_sc(const gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
     const int nt = v2_pick_nt<S, C>(pl);
-    if (nt == V2Menu<S>::nt[0]) return launch_v2_t<S, C, V2Menu<S>::nt[0]>(q, st);
-    if (nt == V2Menu<S>::nt[1]) return launch_v2_t<S, C, V2Menu<S>::nt[1]>(q, st);
+    if (nt == V2Menu<S>::nt[0]) return launch_v2_t<S, C, V2Menu<S>::nt[0]>(pl, q, st);
+    if (nt == V2Menu<S>::nt[1]) return launch_v2_t<S, C, V2Menu<S>::nt[1]>(pl, q, st);
     if constexpr (V2Menu<S>::n > 2) {
-        if (nt == V2Menu<S>::nt[2]) return launch_v2_t<S, C, V2Menu<S>::nt[2]>(q, st);
+        if (nt == V2Menu<S>::nt[2]) return launch_v2_t<S, C, V2Menu<S>::nt[2]>(pl, q, st);
     }
     return fail(GATO_EUNSUPPORTED, "K=%d does not fit the one-CTA kernel", pl->K);
 }

@@ -163,7 +163,45 @@ struct SolveParams2 {
     const int* cdst;      // [nnzC] absolute shared-memory float offset of each C non-zero, <0 = dropped
     int nnzG, nnzC;
     int g_diag;           // pattern of G is purely diagonal: Q_k^-1, R_k^-1 are reciprocals
+    int stage_off;        // > 0: float offset of the TMA staging area in shared memory (values of C, G and g
+                          // arrive by cp.async.bulk, the NEXT system's while this one iterates); 0: direct loads
+    int tail_off;         // float offset of the 32-byte control tail: mbarrier | current system | mbarrier parity
 };
+
+// ---- TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier) ---------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// A bulk copy needs 16-byte aligned addresses and sizes; rows of a [nsys][n] float array are only
+// 4-byte aligned, so the copy covers the enclosing 16-byte words (at most 12 bytes either side, inside
+// words that hold row data) and the consumer skips `lead` floats.
+struct StageSpan { const char* src; uint32_t bytes; int lead; };
+__device__ __forceinline__ StageSpan stage_span(const float* row, int n) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(row), a0 = a & ~(uintptr_t)15;
+    StageSpan sp;
+    sp.src = reinterpret_cast<const char*>(a0);
+    sp.lead = (int)((a - a0) >> 2);
+    sp.bytes = n > 0 ? (uint32_t)(((a - a0) + 4u * (uint32_t)n + 15u) & ~15u) : 0u;
+    return sp;
+}
+__host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   // floats reserved for a row of n
 
 
 // NT = threads per CTA (a multiple of 32, >= LPK * K).  The register file is split over the four SM
@@ -180,641 +218,663 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     constexpr int NW = NT / 32, NKP = NW * L::KPW, NW4 = (NW + 3) / 4;
     extern __shared__ __align__(16) float smem[];
     const SolveParams& p = q.p;
-
     const int K = p.K;
-    const int sys = blockIdx.x;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int lik = lane % LPK;                     // lane in knot
-    const int b = warp * L::KPW + lane / LPK;       // knot / block row owned by this lane group
-    const bool active = b < K;
-    const int h = lik % H, g = lik / H;             // column group, row group (matrix mapping)
-
-    // ---- shared memory carve-up ----------------------------------------------------------------
-    float* kn = smem + (active ? b : 0) * KN;          // this knot's region
-    float* xp = smem + K * KN;                         // p  with one-knot halos  [(NKP+2) VS]
-    float* xt = xp + (NKP + 2) * VS;                   // t  with one-knot halos  [(NKP+2) VS]
-    float* xr = xt + (NKP + 2) * VS;                   // r  (own knot only)      [NKP VS]
-    float* xz = xr + NKP * VS;                         // z  (own knot only)      [NKP VS]
-    float* redA = xz + NKP * VS;                       // per-warp partials of p.Sp    [32]
-    float* redB = redA + 32;                           // per-warp partials of r.P^-1r [32]
-    const int nfloats = L::smem_floats(K, NT);
-
-    // rows of the iterates (and of the Schur-phase row work) owned by this lane: OWN consecutive
-    // positions starting at po0
-    const int po0 = L::own_valid(lik, 0) ? L::pos(L::own_row(lik, 0)) : 0;
-    int orow[OWN];
-    bool ovr[OWN], ov[OWN];
-#pragma unroll
-    for (int j = 0; j < OWN; ++j) {
-        ovr[j] = L::own_valid(lik, j);
-        orow[j] = ovr[j] ? L::own_row(lik, j) : 0;
-        ov[j] = active && ovr[j];
-    }
-    auto load_own = [&](const float* base, float (&v)[OWN]) {    // base = a VS-long slot in pos layout
-        if constexpr (VEC) {
-            const float4 t = *reinterpret_cast<const float4*>(base + po0);
-            const float e[4] = {t.x, t.y, t.z, t.w};
-#pragma unroll
-            for (int j = 0; j < OWN; ++j) v[j] = e[j];           // pad positions hold zeros
-        } else {
-#pragma unroll
-            for (int j = 0; j < OWN; ++j) v[j] = ovr[j] ? base[po0 + j] : 0.f;
-        }
+    // The persistent loop carries NO register across a system: its state (current system, mbarrier parity)
+    // lives in the control tail of shared memory, so the PCG loop keeps the whole register file.
+    // TMA staging of the value arrays (the batched path): one thread issues three bulk copies per system;
+    // the copy for the NEXT system of this persistent CTA is in flight during the PCG loop.
+    const bool staged = q.stage_off > 0;
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + q.tail_off);
+    volatile int* ctl = reinterpret_cast<volatile int*>(smem + q.tail_off + 2);
+    auto issue_stage = [&](int s_) {   // one thread only
+        float* stC_ = smem + q.stage_off;
+        float* stG_ = stC_ + stage_len(q.nnzC);
+        float* stg_ = stG_ + stage_len(q.nnzG);
+        const StageSpan c_ = stage_span(p.C_val + (long long)s_ * p.ldC, q.nnzC);
+        const StageSpan g_ = stage_span(p.G_val + (long long)s_ * p.ldG, q.nnzG);
+        const StageSpan v_ = stage_span(p.g + (long long)s_ * p.ldg, (S + C) * K - C);
+        mbar_expect_tx(mbar, c_.bytes + g_.bytes + v_.bytes);
+        if (c_.bytes) bulk_g2s(stC_, c_.src, c_.bytes, mbar);
+        if (g_.bytes) bulk_g2s(stG_, g_.src, g_.bytes, mbar);
+        if (v_.bytes) bulk_g2s(stg_, v_.src, v_.bytes, mbar);
     };
-    auto store_own = [&](float* base, const float (&v)[OWN]) {   // entries of invalid rows are zero
-        if (!active) return;
-        if constexpr (VEC) {
-            *reinterpret_cast<float4*>(base + po0) = make_float4(v[0], v[1], v[2], v[OWN - 1]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < OWN; ++j)
-                if (ovr[j]) base[po0 + j] = v[j];
+    if (threadIdx.x == 0) {
+        ctl[0] = blockIdx.x;
+        ctl[1] = 0;
+        if (staged) {
+            mbar_init(mbar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            if ((int)blockIdx.x < p.nsys) issue_stage(blockIdx.x);
         }
-    };
-
-    stamp(p, 0);
-    {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0
-        float4* s4 = reinterpret_cast<float4*>(smem);
-        for (int i = tid; i < nfloats / 4; i += NT) s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     __syncthreads();
-    stamp(p, 1);
 
-    const float* Gv = p.G_val + (long long)sys * p.ldG;
-    const float* Cv = p.C_val + (long long)sys * p.ldC;
-    const float* gv = p.g + (long long)sys * p.ldg;
-    const float* cv = p.c + (long long)sys * p.ldc;
-
-    // ==== 1. unpack: coalesced reads of the CSR values, scatter into the dense per-knot blocks ====
-    // One CTA per SM means HBM latency is hidden only by the loads each thread keeps in flight: every
-    // round issues UB (map, value) pairs per thread before the first dependent store.
-    {
-        constexpr int UB = 16;
+    // persistent: CTA i solves systems i, i + gridDim.x, ...
 #pragma unroll 1
-        for (int t0 = tid; t0 < q.nnzC; t0 += NT * UB) {
-            int m[UB];
-            float v[UB];
+    while (true) {
+        int sys = ctl[0];
+        if (sys >= p.nsys) break;
+        // Everything below is recomputed per system from an opaque zero, so that the compiler cannot
+        // hoist per-thread address arithmetic out of the persistent loop and keep it live (spilled)
+        // across the PCG loop: each system compiles like a straight-line kernel.
+        int opaque;
+        asm volatile("mov.u32 %0, 0;" : "=r"(opaque));
+
+        const int tid = (int)threadIdx.x + opaque, warp = tid >> 5, lane = tid & 31;
+        const int lik = lane % LPK;                     // lane in knot
+        const int b = warp * L::KPW + lane / LPK;       // knot / block row owned by this lane group
+        const bool active = b < K;
+        const int h = lik % H, g = lik / H;             // column group, row group (matrix mapping)
+
+        // ---- shared memory carve-up ----------------------------------------------------------------
+        float* kn = smem + (active ? b : 0) * KN;          // this knot's region
+        float* xp = smem + K * KN;                         // p  with one-knot halos  [(NKP+2) VS]
+        float* xt = xp + (NKP + 2) * VS;                   // t  with one-knot halos  [(NKP+2) VS]
+        float* xr = xt + (NKP + 2) * VS;                   // r  (own knot only)      [NKP VS]
+        float* xz = xr + NKP * VS;                         // z  (own knot only)      [NKP VS]
+        float* redA = xz + NKP * VS;                       // per-warp partials of p.Sp    [32]
+        float* redB = redA + 32;                           // per-warp partials of r.P^-1r [32]
+        const int nfloats = L::smem_floats(K, NT);
+
+        // rows of the iterates (and of the Schur-phase row work) owned by this lane: OWN consecutive
+        // positions starting at po0
+        const int po0 = L::own_valid(lik, 0) ? L::pos(L::own_row(lik, 0)) : 0;
+        int orow[OWN];
+        bool ovr[OWN], ov[OWN];
 #pragma unroll
-            for (int u = 0; u < UB; ++u) {
-                const int t = t0 + u * NT;
-                m[u] = -1;
-                v[u] = 0.f;
-                if (t < q.nnzC) { m[u] = __ldg(q.cdst + t); v[u] = __ldg(Cv + t); }
-            }
-#pragma unroll
-            for (int u = 0; u < UB; ++u)
-                if (m[u] >= 0) smem[m[u]] = v[u];
+        for (int j = 0; j < OWN; ++j) {
+            ovr[j] = L::own_valid(lik, j);
+            orow[j] = ovr[j] ? L::own_row(lik, j) : 0;
+            ov[j] = active && ovr[j];
         }
-        constexpr int UG = 8;
-        const int n_z = (S + C) * K - C;
-#pragma unroll 1
-        for (int t0 = tid; t0 < max(q.nnzG, n_z); t0 += NT * UG) {
-            int m[UG];
-            float v[UG], w[UG];
+        auto load_own = [&](const float* base, float (&v)[OWN]) {    // base = a VS-long slot in pos layout
+            if constexpr (VEC) {
+                const float4 t = *reinterpret_cast<const float4*>(base + po0);
+                const float e[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
-            for (int u = 0; u < UG; ++u) {
-                const int t = t0 + u * NT;
-                m[u] = -1;
-                v[u] = w[u] = 0.f;
-                if (t < q.nnzG) { m[u] = __ldg(q.gdst + t); v[u] = __ldg(Gv + t); }
-                if (t < n_z) w[u] = __ldg(gv + t);
+                for (int j = 0; j < OWN; ++j) v[j] = e[j];           // pad positions hold zeros
+            } else {
+#pragma unroll
+                for (int j = 0; j < OWN; ++j) v[j] = ovr[j] ? base[po0 + j] : 0.f;
             }
+        };
+        auto store_own = [&](float* base, const float (&v)[OWN]) {   // entries of invalid rows are zero
+            if (!active) return;
+            if constexpr (VEC) {
+                *reinterpret_cast<float4*>(base + po0) = make_float4(v[0], v[1], v[2], v[OWN - 1]);
+            } else {
 #pragma unroll
-            for (int u = 0; u < UG; ++u) {
-                const int t = t0 + u * NT;
-                if (m[u] >= 0) smem[m[u] & kMapMask] = v[u] + ((m[u] & kMapDiagBit) ? p.rho : 0.0f);
-                if (t < n_z) {   // g -> per-knot q (pos layout) | r
-                    const int k = t / (S + C), o = t - k * (S + C);
-                    smem[k * KN + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = w[u];
+                for (int j = 0; j < OWN; ++j)
+                    if (ovr[j]) base[po0 + j] = v[j];
+            }
+        };
+
+        stamp(p, 0);
+        {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0
+            float4* s4 = reinterpret_cast<float4*>(smem);
+            for (int i = tid; i < nfloats / 4; i += NT) s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+        stamp(p, 1);
+
+        const float* cv = p.c + (long long)sys * p.ldc;
+        // value sources: the staging area once this system's bulk copies have landed, else global memory
+        const float* Gv = p.G_val + (long long)sys * p.ldG;
+        const float* Cv = p.C_val + (long long)sys * p.ldC;
+        const float* gv = p.g + (long long)sys * p.ldg;
+        if (staged) {
+            const float* stC = smem + q.stage_off + opaque;
+            const float* stG = stC + stage_len(q.nnzC);
+            const float* stg = stG + stage_len(q.nnzG);
+            Cv = stC + stage_span(Cv, q.nnzC).lead;
+            Gv = stG + stage_span(Gv, q.nnzG).lead;
+            gv = stg + stage_span(gv, (S + C) * K - C).lead;
+            mbar_wait(mbar, (uint32_t)ctl[1]);
+        }
+
+        // ==== 1. unpack: coalesced reads of the CSR values, scatter into the dense per-knot blocks ====
+        // One CTA per SM means memory latency is hidden only by the loads each thread keeps in flight:
+        // every round issues UB (map, value) pairs per thread before the first dependent store.
+        {
+            constexpr int UB = 16;
+#pragma unroll 1
+            for (int t0 = tid; t0 < q.nnzC; t0 += NT * UB) {
+                int m[UB];
+                float v[UB];
+#pragma unroll
+                for (int u = 0; u < UB; ++u) {
+                    const int t = t0 + u * NT;
+                    m[u] = -1;
+                    v[u] = 0.f;
+                    if (t < q.nnzC) { m[u] = __ldg(q.cdst + t); v[u] = Cv[t]; }
+                }
+#pragma unroll
+                for (int u = 0; u < UB; ++u)
+                    if (m[u] >= 0) smem[m[u]] = v[u];
+            }
+            constexpr int UG = 8;
+            const int n_z = (S + C) * K - C;
+#pragma unroll 1
+            for (int t0 = tid; t0 < max(q.nnzG, n_z); t0 += NT * UG) {
+                int m[UG];
+                float v[UG], w[UG];
+#pragma unroll
+                for (int u = 0; u < UG; ++u) {
+                    const int t = t0 + u * NT;
+                    m[u] = -1;
+                    v[u] = w[u] = 0.f;
+                    if (t < q.nnzG) { m[u] = __ldg(q.gdst + t); v[u] = Gv[t]; }
+                    if (t < n_z) w[u] = gv[t];
+                }
+#pragma unroll
+                for (int u = 0; u < UG; ++u) {
+                    const int t = t0 + u * NT;
+                    if (m[u] >= 0) smem[m[u] & kMapMask] = v[u] + ((m[u] & kMapDiagBit) ? p.rho : 0.0f);
+                    if (t < n_z) {   // g -> per-knot q (pos layout) | r
+                        const int k = t / (S + C), o = t - k * (S + C);
+                        smem[k * KN + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = w[u];
+                    }
                 }
             }
         }
-    }
-    __syncthreads();
-    stamp(p, 2);
+        __syncthreads();
+        if (staged && tid == 0 && sys + (int)gridDim.x < p.nsys) {
+            // the staging area has been consumed (barrier above): fetch the next system's values now, so
+            // they arrive while this system iterates.  Generic-proxy reads -> async-proxy writes.
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue_stage(sys + (int)gridDim.x);
+        }
+        stamp(p, 2);
 
-    // ---- Schur-phase helpers (own-row mapping) -----------------------------------------------------
-    // row `row` of a row-major [.][VS] matrix in pos layout -> registers indexed by true column
-    auto load_row = [&](const float* rowbase, float (&v)[S]) {
+        // ---- Schur-phase helpers (own-row mapping) -----------------------------------------------------
+        // row `row` of a row-major [.][VS] matrix in pos layout -> registers indexed by true column
+        auto load_row = [&](const float* rowbase, float (&v)[S]) {
 #pragma unroll
-        for (int ci = 0; ci < VS / 4; ++ci) {
-            const float4 t = reinterpret_cast<const float4*>(rowbase)[ci];
-            const float e[4] = {t.x, t.y, t.z, t.w};
+            for (int ci = 0; ci < VS / 4; ++ci) {
+                const float4 t = reinterpret_cast<const float4*>(rowbase)[ci];
+                const float e[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (L::pos_valid(4 * ci + u)) v[L::pos_row(4 * ci + u)] = e[u];
-        }
-    };
-    auto store_row = [&](float* rowbase, const float (&v)[S]) {
+                for (int u = 0; u < 4; ++u)
+                    if (L::pos_valid(4 * ci + u)) v[L::pos_row(4 * ci + u)] = e[u];
+            }
+        };
+        auto store_row = [&](float* rowbase, const float (&v)[S]) {
 #pragma unroll
-        for (int ci = 0; ci < VS / 4; ++ci) {
-            float e[4];
+            for (int ci = 0; ci < VS / 4; ++ci) {
+                float e[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) e[u] = L::pos_valid(4 * ci + u) ? v[L::pos_row(4 * ci + u)] : 0.f;
-            reinterpret_cast<float4*>(rowbase)[ci] = make_float4(e[0], e[1], e[2], e[3]);
-        }
-    };
-    // out[i][c] += sum_k X[row_i, k] * Y[c, k]:  X = [k][VS] with rows in pos layout (own rows are
-    // one aligned load), Y = [k][VS] with its first index in pos layout (a whole column per k)
-    auto rank1_S = [&](float (&out)[OWN][S], const float* X, const float* Y, int nk) {
+                for (int u = 0; u < 4; ++u) e[u] = L::pos_valid(4 * ci + u) ? v[L::pos_row(4 * ci + u)] : 0.f;
+                reinterpret_cast<float4*>(rowbase)[ci] = make_float4(e[0], e[1], e[2], e[3]);
+            }
+        };
+        // out[i][c] += sum_k X[row_i, k] * Y[c, k]:  X = [k][VS] with rows in pos layout (own rows are
+        // one aligned load), Y = [k][VS] with its first index in pos layout (a whole column per k)
+        auto rank1_S = [&](float (&out)[OWN][S], const float* X, const float* Y, int nk) {
 #pragma unroll 1
-        for (int k = 0; k < nk; ++k) {
-            float xv[OWN], yv[S];
-            load_own(X + k * VS, xv);
-            load_row(Y + k * VS, yv);
+            for (int k = 0; k < nk; ++k) {
+                float xv[OWN], yv[S];
+                load_own(X + k * VS, xv);
+                load_row(Y + k * VS, yv);
+#pragma unroll
+                for (int i = 0; i < OWN; ++i)
+#pragma unroll
+                    for (int c = 0; c < S; ++c) out[i][c] = fmaf(xv[i], yv[c], out[i][c]);
+            }
+        };
+        // same with a C-wide output; Y = [k][LDC] plain
+        auto rank1_C = [&](float (&out)[OWN][C], const float* X, const float* Y, int nk) {
+#pragma unroll 1
+            for (int k = 0; k < nk; ++k) {
+                float xv[OWN];
+                load_own(X + k * VS, xv);
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const float y = Y[k * LDC + c];
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i) out[i][c] = fmaf(xv[i], y, out[i][c]);
+                }
+            }
+        };
+
+        // ==== 2./3. two passes through ONE copy of the elimination code: pass 0 inverts Q_b (and R_b),
+        //      pass 1 forms block row b (phi_b, gamma_b, theta_b) and inverts theta_b.
+        //   phi_b = A Q^-1, BR = B R^-1 (stage b-1), theta_b = phi A^T + Q_b^-1 + BR B^T,
+        //   gamma_b = Q_b^-1 q_b - c_b + phi q_{b-1} + BR r_{b-1}          (src/gato_schur.cuh:277-385)
+        float a[OWN][S];       // rows being inverted; the shuffles need the whole warp, idle lanes carry an identity
+        float th[OWN][S];      // theta_b rows (kept for the S main block)
+        float gam[OWN];
+#pragma unroll
+        for (int i = 0; i < OWN; ++i) {
+            gam[i] = 0.f;
+#pragma unroll
+            for (int j = 0; j < S; ++j) th[i][j] = 0.f;
+        }
+#pragma unroll 1
+        for (int pass = 0; pass < 2; ++pass) {
 #pragma unroll
             for (int i = 0; i < OWN; ++i)
 #pragma unroll
-                for (int c = 0; c < S; ++c) out[i][c] = fmaf(xv[i], yv[c], out[i][c]);
-        }
-    };
-    // same with a C-wide output; Y = [k][LDC] plain
-    auto rank1_C = [&](float (&out)[OWN][C], const float* X, const float* Y, int nk) {
-#pragma unroll 1
-        for (int k = 0; k < nk; ++k) {
-            float xv[OWN];
-            load_own(X + k * VS, xv);
-#pragma unroll
-            for (int c = 0; c < C; ++c) {
-                const float y = Y[k * LDC + c];
-#pragma unroll
-                for (int i = 0; i < OWN; ++i) out[i][c] = fmaf(xv[i], y, out[i][c]);
-            }
-        }
-    };
-
-    // ==== 2./3. two passes through ONE copy of the elimination code: pass 0 inverts Q_b (and R_b),
-    //      pass 1 forms block row b (phi_b, gamma_b, theta_b) and inverts theta_b.
-    //   phi_b = A Q^-1, BR = B R^-1 (stage b-1), theta_b = phi A^T + Q_b^-1 + BR B^T,
-    //   gamma_b = Q_b^-1 q_b - c_b + phi q_{b-1} + BR r_{b-1}          (src/gato_schur.cuh:277-385)
-    float a[OWN][S];       // rows being inverted; the shuffles need the whole warp, idle lanes carry an identity
-    float th[OWN][S];      // theta_b rows (kept for the S main block)
-    float gam[OWN];
-#pragma unroll
-    for (int i = 0; i < OWN; ++i) {
-        gam[i] = 0.f;
-#pragma unroll
-        for (int j = 0; j < S; ++j) th[i][j] = 0.f;
-    }
-#pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
-#pragma unroll
-        for (int i = 0; i < OWN; ++i)
-#pragma unroll
-            for (int j = 0; j < S; ++j) a[i][j] = (!active && MS::row(lik, i) == j) ? 1.f : 0.f;
-        if (pass == 0) {
-            if (active && b == 0) {   // block row 0 keeps raw Q0 as theta_0^-1 (src/gato_schur.cuh:75-81): stash it
-#pragma unroll
-                for (int i = 0; i < OWN; ++i)
-                    if (ovr[i]) {
-#pragma unroll
-                        for (int ci = 0; ci < VS / 4; ++ci)
-                            reinterpret_cast<float4*>(kn + L::oPhi + orow[i] * VS)[ci] =
-                                reinterpret_cast<const float4*>(kn + L::oQ + orow[i] * VS)[ci];
-                    }
-            }
-            if (q.g_diag) {   // diagonal cost blocks: the inverses are reciprocals (same bits as the elimination)
-                if (active) {
+                for (int j = 0; j < S; ++j) a[i][j] = (!active && MS::row(lik, i) == j) ? 1.f : 0.f;
+            if (pass == 0) {
+                if (active && b == 0) {   // block row 0 keeps raw Q0 as theta_0^-1 (src/gato_schur.cuh:75-81): stash it
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
                         if (ovr[i]) {
-                            float* d = kn + L::oQ + orow[i] * VS + po0 + i;
-                            *d = 1.0f / *d;
-                        }
-                    if (b < K - 1) {
 #pragma unroll
-                        for (int i = 0; i < OWNC; ++i) {
-                            const int row = MC::row(lik, i);
-                            if (row >= 0) {
-                                float* d = kn + L::oR + row * LDC + row;
+                            for (int ci = 0; ci < VS / 4; ++ci)
+                                reinterpret_cast<float4*>(kn + L::oPhi + orow[i] * VS)[ci] =
+                                    reinterpret_cast<const float4*>(kn + L::oQ + orow[i] * VS)[ci];
+                        }
+                }
+                if (q.g_diag) {   // diagonal cost blocks: the inverses are reciprocals (same bits as the elimination)
+                    if (active) {
+#pragma unroll
+                        for (int i = 0; i < OWN; ++i)
+                            if (ovr[i]) {
+                                float* d = kn + L::oQ + orow[i] * VS + po0 + i;
                                 *d = 1.0f / *d;
+                            }
+                        if (b < K - 1) {
+#pragma unroll
+                            for (int i = 0; i < OWNC; ++i) {
+                                const int row = MC::row(lik, i);
+                                if (row >= 0) {
+                                    float* d = kn + L::oR + row * LDC + row;
+                                    *d = 1.0f / *d;
+                                }
                             }
                         }
                     }
+                    __syncthreads();
+                    stamp(p, 3);
+                    continue;
                 }
-                __syncthreads();
-                stamp(p, 3);
-                continue;
-            }
-            if (active) {
+                if (active) {
 #pragma unroll
-                for (int i = 0; i < OWN; ++i)
-                    if (ovr[i]) load_row(kn + L::oQ + orow[i] * VS, a[i]);
-            }
-        } else if (active) {
-            if (b == 0) {
+                    for (int i = 0; i < OWN; ++i)
+                        if (ovr[i]) load_row(kn + L::oQ + orow[i] * VS, a[i]);
+                }
+            } else if (active) {
+                if (b == 0) {
 #pragma unroll
-                for (int i = 0; i < OWN; ++i)
-                    if (ovr[i]) {
-                        float qv[S];
-                        load_row(kn + L::oQ + orow[i] * VS, a[i]);     // theta_0 = Q0^-1 (:26-149)
-                        load_row(kn + L::oq, qv);
-                        float acc = 0.f;
+                    for (int i = 0; i < OWN; ++i)
+                        if (ovr[i]) {
+                            float qv[S];
+                            load_row(kn + L::oQ + orow[i] * VS, a[i]);     // theta_0 = Q0^-1 (:26-149)
+                            load_row(kn + L::oq, qv);
+                            float acc = 0.f;
 #pragma unroll
-                        for (int k = 0; k < S; ++k) acc = fmaf(a[i][k], qv[k], acc);
-                        gam[i] = acc;                                  // c[0:S] is ignored
+                            for (int k = 0; k < S; ++k) acc = fmaf(a[i][k], qv[k], acc);
+                            gam[i] = acc;                                  // c[0:S] is ignored
+                        }
+                } else {
+                    const float* prev = kn - KN;
+                    float phi[OWN][S], br[OWN][C];
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i) {
+#pragma unroll
+                        for (int c = 0; c < S; ++c) phi[i][c] = 0.f;
+#pragma unroll
+                        for (int c = 0; c < C; ++c) br[i][c] = 0.f;
                     }
-            } else {
-                const float* prev = kn - KN;
-                float phi[OWN][S], br[OWN][C];
+                    if (q.g_diag) {
 #pragma unroll
-                for (int i = 0; i < OWN; ++i) {
+                        for (int c = 0; c < S; ++c) {
+                            float xv[OWN];
+                            load_own(prev + L::oA + c * VS, xv);
+                            const float qi = prev[L::oQ + c * VS + L::pos(c)];
 #pragma unroll
-                    for (int c = 0; c < S; ++c) phi[i][c] = 0.f;
+                            for (int i = 0; i < OWN; ++i) phi[i][c] = xv[i] * qi;
+                        }
 #pragma unroll
-                    for (int c = 0; c < C; ++c) br[i][c] = 0.f;
-                }
-                if (q.g_diag) {
+                        for (int c = 0; c < C; ++c) {
+                            float xv[OWN];
+                            load_own(prev + L::oB + c * VS, xv);
+                            const float ri = prev[L::oR + c * LDC + c];
+#pragma unroll
+                            for (int i = 0; i < OWN; ++i) br[i][c] = xv[i] * ri;
+                        }
+                    } else {
+                        rank1_S(phi, prev + L::oA, prev + L::oQ, S);
+                        rank1_C(br, prev + L::oB, prev + L::oR, C);
+                    }
 #pragma unroll
                     for (int c = 0; c < S; ++c) {
-                        float xv[OWN];
-                        load_own(prev + L::oA + c * VS, xv);
-                        const float qi = prev[L::oQ + c * VS + L::pos(c)];
+                        float col[OWN];
 #pragma unroll
-                        for (int i = 0; i < OWN; ++i) phi[i][c] = xv[i] * qi;
+                        for (int i = 0; i < OWN; ++i) col[i] = phi[i][c];
+                        store_own(kn + L::oPhi + c * VS, col);
                     }
+                    {
+                        float qv[S], qp[S];
+                        load_row(kn + L::oq, qv);
+                        load_row(prev + L::oq, qp);
 #pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        float xv[OWN];
-                        load_own(prev + L::oB + c * VS, xv);
-                        const float ri = prev[L::oR + c * LDC + c];
+                        for (int i = 0; i < OWN; ++i)
+                            if (ovr[i]) {
+                                float qrow[S];
+                                load_row(kn + L::oQ + orow[i] * VS, qrow);
+                                float a0 = 0.f, a1 = 0.f, a2 = 0.f;
 #pragma unroll
-                        for (int i = 0; i < OWN; ++i) br[i][c] = xv[i] * ri;
+                                for (int k = 0; k < S; ++k) {
+                                    a0 = fmaf(qrow[k], qv[k], a0);
+                                    a1 = fmaf(phi[i][k], qp[k], a1);
+                                    a[i][k] = 0.f;
+                                }
+#pragma unroll
+                                for (int k = 0; k < C; ++k) a2 = fmaf(br[i][k], prev[L::or_ + k], a2);
+                                gam[i] = (a0 - __ldg(cv + b * S + orow[i])) + (a2 + a1);
+                            }
                     }
-                } else {
-                    rank1_S(phi, prev + L::oA, prev + L::oQ, S);
-                    rank1_C(br, prev + L::oB, prev + L::oR, C);
-                }
-#pragma unroll
-                for (int c = 0; c < S; ++c) {
-                    float col[OWN];
-#pragma unroll
-                    for (int i = 0; i < OWN; ++i) col[i] = phi[i][c];
-                    store_own(kn + L::oPhi + c * VS, col);
-                }
-                {
-                    float qv[S], qp[S];
-                    load_row(kn + L::oq, qv);
-                    load_row(prev + L::oq, qp);
+                    rank1_S(a, kn + L::oPhi, prev + L::oA, S);             // phi A^T
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
                         if (ovr[i]) {
                             float qrow[S];
                             load_row(kn + L::oQ + orow[i] * VS, qrow);
-                            float a0 = 0.f, a1 = 0.f, a2 = 0.f;
 #pragma unroll
-                            for (int k = 0; k < S; ++k) {
-                                a0 = fmaf(qrow[k], qv[k], a0);
-                                a1 = fmaf(phi[i][k], qp[k], a1);
-                                a[i][k] = 0.f;
-                            }
-#pragma unroll
-                            for (int k = 0; k < C; ++k) a2 = fmaf(br[i][k], prev[L::or_ + k], a2);
-                            gam[i] = (a0 - __ldg(cv + b * S + orow[i])) + (a2 + a1);
+                            for (int c = 0; c < S; ++c) a[i][c] += qrow[c];   // + Q_b^-1
                         }
+#pragma unroll
+                    for (int k = 0; k < C; ++k) {                          // + BR B^T
+                        float yv[S];
+                        load_row(prev + L::oB + k * VS, yv);
+#pragma unroll
+                        for (int i = 0; i < OWN; ++i)
+#pragma unroll
+                            for (int c = 0; c < S; ++c) a[i][c] = fmaf(br[i][k], yv[c], a[i][c]);
+                    }
                 }
-                rank1_S(a, kn + L::oPhi, prev + L::oA, S);             // phi A^T
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
-                    if (ovr[i]) {
-                        float qrow[S];
-                        load_row(kn + L::oQ + orow[i] * VS, qrow);
 #pragma unroll
-                        for (int c = 0; c < S; ++c) a[i][c] += qrow[c];   // + Q_b^-1
-                    }
-#pragma unroll
-                for (int k = 0; k < C; ++k) {                          // + BR B^T
-                    float yv[S];
-                    load_row(prev + L::oB + k * VS, yv);
+                    for (int j = 0; j < S; ++j) th[i][j] = a[i][j];
+            }
+            gj_invert_knot<MS, LPK>(a, lik, lane);
+            if (pass == 0) {
+                if (active) {
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
-#pragma unroll
-                        for (int c = 0; c < S; ++c) a[i][c] = fmaf(br[i][k], yv[c], a[i][c]);
+                        if (ovr[i]) store_row(kn + L::oQ + orow[i] * VS, a[i]);
                 }
+                const bool hasR = active && b < K - 1;
+                float c2[OWNC][C];
+#pragma unroll
+                for (int i = 0; i < OWNC; ++i) {
+                    const int row = MC::row(lik, i);
+#pragma unroll
+                    for (int j = 0; j < C; ++j)
+                        c2[i][j] = (hasR && row >= 0) ? kn[L::oR + row * LDC + j] : (!hasR && j == row ? 1.f : 0.f);
+                }
+                gj_invert_knot<MC, LPK>(c2, lik, lane);
+#pragma unroll
+                for (int i = 0; i < OWNC; ++i) {
+                    const int row = MC::row(lik, i);
+                    if (hasR && row >= 0) {
+#pragma unroll
+                        for (int j = 0; j < C; ++j) kn[L::oR + row * LDC + j] = c2[i][j];
+                    }
+                }
+                __syncthreads();   // every stage's A, B, Q^-1, R^-1, q, r are in shared memory
+                stamp(p, 3);
             }
+        }
+        // a = theta_b^-1 rows; block row 0 uses raw Q0 instead (the reference's Pinv[0] = Q0)
+        if (active && b == 0) {
 #pragma unroll
             for (int i = 0; i < OWN; ++i)
-#pragma unroll
-                for (int j = 0; j < S; ++j) th[i][j] = a[i][j];
+                if (ovr[i]) load_row(kn + L::oPhi + orow[i] * VS, a[i]);
         }
-        gj_invert_knot<MS, LPK>(a, lik, lane);
-        if (pass == 0) {
-            if (active) {
-#pragma unroll
-                for (int i = 0; i < OWN; ++i)
-                    if (ovr[i]) store_row(kn + L::oQ + orow[i] * VS, a[i]);
-            }
-            const bool hasR = active && b < K - 1;
-            float c2[OWNC][C];
-#pragma unroll
-            for (int i = 0; i < OWNC; ++i) {
-                const int row = MC::row(lik, i);
-#pragma unroll
-                for (int j = 0; j < C; ++j)
-                    c2[i][j] = (hasR && row >= 0) ? kn[L::oR + row * LDC + j] : (!hasR && j == row ? 1.f : 0.f);
-            }
-            gj_invert_knot<MC, LPK>(c2, lik, lane);
-#pragma unroll
-            for (int i = 0; i < OWNC; ++i) {
-                const int row = MC::row(lik, i);
-                if (hasR && row >= 0) {
-#pragma unroll
-                    for (int j = 0; j < C; ++j) kn[L::oR + row * LDC + j] = c2[i][j];
-                }
-            }
-            __syncthreads();   // every stage's A, B, Q^-1, R^-1, q, r are in shared memory
-            stamp(p, 3);
-        }
-    }
-    // a = theta_b^-1 rows; block row 0 uses raw Q0 instead (the reference's Pinv[0] = Q0)
-    if (active && b == 0) {
-#pragma unroll
-        for (int i = 0; i < OWN; ++i)
-            if (ovr[i]) load_row(kn + L::oPhi + orow[i] * VS, a[i]);
-    }
-    stamp(p, 4);
-    __syncthreads();   // phi_b of every block row is in shared memory
+        stamp(p, 4);
+        __syncthreads();   // phi_b of every block row is in shared memory
 
-    // ==== 4. iteration matrices into registers, matrix mapping ====================================
-    // Lane (g, h) holds rows g*R .. g*R+R-1 of [S_left | S_main | S_right] restricted to its column
-    // group, and the same rows of theta^-1.  Local column order (H == 2): [side knot (VS positions:
-    // the left knot for h = 0, the right knot for h = 1) | own half of the main block (HALFP)];
-    // (H == 1): [left | main | right], VS positions each.  Pad positions are never touched.
-    constexpr int NLOC = (H == 2) ? VS + HALFP : 3 * VS;
-    constexpr int MAIN0 = VS;                      // first local column of the main block (both layouts)
-    float Sm[R][NLOC], Tm[R][HALFP];
-    {
-        // own-row mapping (OWN rows x all columns) -> matrix mapping (R rows x own column half):
-        // the two lanes of a row group swap the quadrants they do not need
-        auto to_matrix = [&](const float (&own)[OWN][S], float (&mm)[R][HALFP]) {
-#pragma unroll
-            for (int i = 0; i < R; ++i)
-#pragma unroll
-                for (int l = 0; l < HALFP; ++l) mm[i][l] = 0.f;
-            if constexpr (H == 2) {
-#pragma unroll
-                for (int j = 0; j < OWN; ++j)
-#pragma unroll
-                    for (int l = 0; l < HALFU; ++l) {
-                        const float send = h ? own[j][l] : own[j][HALFU + l];
-                        const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
-                        mm[j][l] = h ? recv : own[j][l];                                   // rows [0, OWN)
-                        if (OWN + j < R) mm[OWN + j][l] = h ? own[j][HALFU + l] : recv;    // rows [OWN, R)
-                    }
-            } else {
-#pragma unroll
-                for (int j = 0; j < OWN; ++j)
-#pragma unroll
-                    for (int l = 0; l < S; ++l) mm[j][l] = own[j][l];
-            }
-        };
-#pragma unroll
-        for (int i = 0; i < R; ++i)
-#pragma unroll
-            for (int l = 0; l < NLOC; ++l) Sm[i][l] = 0.f;
+        // ==== 4. iteration matrices into registers, matrix mapping ====================================
+        // Lane (g, h) holds rows g*R .. g*R+R-1 of [S_left | S_main | S_right] restricted to its column
+        // group, and the same rows of theta^-1.  Local column order (H == 2): [side knot (VS positions:
+        // the left knot for h = 0, the right knot for h = 1) | own half of the main block (HALFP)];
+        // (H == 1): [left | main | right], VS positions each.  Pad positions are never touched.
+        constexpr int NLOC = (H == 2) ? VS + HALFP : 3 * VS;
+        constexpr int MAIN0 = VS;                      // first local column of the main block (both layouts)
+        float Sm[R][NLOC], Tm[R][HALFP];
         {
-            float mm[R][HALFP];
-            to_matrix(th, mm);
+            // own-row mapping (OWN rows x all columns) -> matrix mapping (R rows x own column half):
+            // the two lanes of a row group swap the quadrants they do not need
+            auto to_matrix = [&](const float (&own)[OWN][S], float (&mm)[R][HALFP]) {
+#pragma unroll
+                for (int i = 0; i < R; ++i)
+#pragma unroll
+                    for (int l = 0; l < HALFP; ++l) mm[i][l] = 0.f;
+                if constexpr (H == 2) {
+#pragma unroll
+                    for (int j = 0; j < OWN; ++j)
+#pragma unroll
+                        for (int l = 0; l < HALFU; ++l) {
+                            const float send = h ? own[j][l] : own[j][HALFU + l];
+                            const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                            mm[j][l] = h ? recv : own[j][l];                                   // rows [0, OWN)
+                            if (OWN + j < R) mm[OWN + j][l] = h ? own[j][HALFU + l] : recv;    // rows [OWN, R)
+                        }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < OWN; ++j)
+#pragma unroll
+                        for (int l = 0; l < S; ++l) mm[j][l] = own[j][l];
+                }
+            };
 #pragma unroll
             for (int i = 0; i < R; ++i)
 #pragma unroll
-                for (int l = 0; l < HALFP; ++l) Sm[i][MAIN0 + l] = mm[i][l];
-        }
-        to_matrix(a, Tm);
+                for (int l = 0; l < NLOC; ++l) Sm[i][l] = 0.f;
+            {
+                float mm[R][HALFP];
+                to_matrix(th, mm);
+#pragma unroll
+                for (int i = 0; i < R; ++i)
+#pragma unroll
+                    for (int l = 0; l < HALFP; ++l) Sm[i][MAIN0 + l] = mm[i][l];
+            }
+            to_matrix(a, Tm);
 
-        const bool hasL = active && b > 0, hasR = active && b + 1 < K;
-        const float* phiL = kn + L::oPhi;            // phi_b      : S[b,left]  = phi_b
-        const float* phiR = kn + KN + L::oPhi;       // phi_{b+1}  : S[b,right] = phi_{b+1}^T
-        if constexpr (H == 2) {
-            if (h == 0) {
-                if (hasL) {   // phi_b[rr, c] at c*VS + pos(rr): the R rows of group g are contiguous
+            const bool hasL = active && b > 0, hasR = active && b + 1 < K;
+            const float* phiL = kn + L::oPhi;            // phi_b      : S[b,left]  = phi_b
+            const float* phiR = kn + KN + L::oPhi;       // phi_{b+1}  : S[b,right] = phi_{b+1}^T
+            if constexpr (H == 2) {
+                if (h == 0) {
+                    if (hasL) {   // phi_b[rr, c] at c*VS + pos(rr): the R rows of group g are contiguous
 #pragma unroll
-                    for (int c = 0; c < S; ++c) {
+                        for (int c = 0; c < S; ++c) {
 #pragma unroll
-                        for (int ci = 0; ci < HALFP / 4; ++ci) {
-                            const float4 t = reinterpret_cast<const float4*>(phiL + c * VS + g * HALFP)[ci];
+                            for (int ci = 0; ci < HALFP / 4; ++ci) {
+                                const float4 t = reinterpret_cast<const float4*>(phiL + c * VS + g * HALFP)[ci];
+                                const float e[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                                for (int u = 0; u < 4; ++u)
+                                    if (4 * ci + u < R) Sm[4 * ci + u][L::pos(c)] = e[u];
+                            }
+                        }
+                    }
+                } else if (hasR) {   // phi_{b+1}[c, rr] at rr*VS + pos(c): a whole row of S[b,right] is contiguous
+#pragma unroll
+                    for (int i = 0; i < R; ++i) {
+#pragma unroll
+                        for (int ci = 0; ci < VS / 4; ++ci) {
+                            const float4 t = reinterpret_cast<const float4*>(phiR + (g * R + i) * VS)[ci];
                             const float e[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
                             for (int u = 0; u < 4; ++u)
-                                if (4 * ci + u < R) Sm[4 * ci + u][L::pos(c)] = e[u];
+                                if (L::pos_valid(4 * ci + u)) Sm[i][4 * ci + u] = e[u];
                         }
                     }
                 }
-            } else if (hasR) {   // phi_{b+1}[c, rr] at rr*VS + pos(c): a whole row of S[b,right] is contiguous
+            } else {
 #pragma unroll
                 for (int i = 0; i < R; ++i) {
+                    const int rr = g * R + i;
+                    const bool rv = rr < S;
 #pragma unroll
-                    for (int ci = 0; ci < VS / 4; ++ci) {
-                        const float4 t = reinterpret_cast<const float4*>(phiR + (g * R + i) * VS)[ci];
-                        const float e[4] = {t.x, t.y, t.z, t.w};
-#pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            if (L::pos_valid(4 * ci + u)) Sm[i][4 * ci + u] = e[u];
+                    for (int l = 0; l < S; ++l) {
+                        if (rv && hasL) Sm[i][l] = phiL[l * VS + rr];
+                        if (rv && hasR) Sm[i][2 * VS + l] = phiR[rr * VS + l];
                     }
                 }
             }
-        } else {
-#pragma unroll
-            for (int i = 0; i < R; ++i) {
-                const int rr = g * R + i;
-                const bool rv = rr < S;
-#pragma unroll
-                for (int l = 0; l < S; ++l) {
-                    if (rv && hasL) Sm[i][l] = phiL[l * VS + rr];
-                    if (rv && hasR) Sm[i][2 * VS + l] = phiR[rr * VS + l];
-                }
-            }
         }
-    }
-    stamp(p, 5);
+        stamp(p, 5);
 
-    // ---- iterate plumbing ------------------------------------------------------------------------
-    auto scatter = [&](const float (&acc)[R], float (&out)[OWN]) {   // combine the H column groups
-        if (H == 2) {
+        // ---- iterate plumbing ------------------------------------------------------------------------
+        auto scatter = [&](const float (&acc)[R], float (&out)[OWN]) {   // combine the H column groups
+            if (H == 2) {
 #pragma unroll
-            for (int j = 0; j < OWN; ++j) {   // h = 0 keeps rows [0, OWN), h = 1 keeps rows [OWN, R)
-                const float hi = (OWN + j < R) ? acc[OWN + j] : 0.f;
-                const float send = h ? acc[j] : hi;
-                const float mine = h ? hi : acc[j];
-                out[j] = mine + __shfl_xor_sync(0xffffffffu, send, 1);
+                for (int j = 0; j < OWN; ++j) {   // h = 0 keeps rows [0, OWN), h = 1 keeps rows [OWN, R)
+                    const float hi = (OWN + j < R) ? acc[OWN + j] : 0.f;
+                    const float send = h ? acc[j] : hi;
+                    const float mine = h ? hi : acc[j];
+                    out[j] = mine + __shfl_xor_sync(0xffffffffu, send, 1);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < OWN; ++j) out[j] = acc[j];
             }
-        } else {
+        };
+        // rows of [S_left | S_main | S_right] against x (halo layout: knot k at slot k + 1)
+        auto apply_S = [&](const float* x, float (&out)[OWN]) {
+            float acc[R];
 #pragma unroll
-            for (int j = 0; j < OWN; ++j) out[j] = acc[j];
-        }
-    };
-    // rows of [S_left | S_main | S_right] against x (halo layout: knot k at slot k + 1)
-    auto apply_S = [&](const float* x, float (&out)[OWN]) {
-        float acc[R];
+            for (int i = 0; i < R; ++i) acc[i] = 0.f;
+            if (H == 2) {
+                const float4* side = reinterpret_cast<const float4*>(x + (b + 2 * h) * VS);
+                const float4* mainh = reinterpret_cast<const float4*>(x + (b + 1) * VS + h * HALFP);
 #pragma unroll
-        for (int i = 0; i < R; ++i) acc[i] = 0.f;
-        if (H == 2) {
-            const float4* side = reinterpret_cast<const float4*>(x + (b + 2 * h) * VS);
-            const float4* mainh = reinterpret_cast<const float4*>(x + (b + 1) * VS + h * HALFP);
+                for (int ci = 0; ci < VS / 4; ++ci) {
+                    const float4 v = side[ci];
+                    const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-            for (int ci = 0; ci < VS / 4; ++ci) {
-                const float4 v = side[ci];
-                const float e[4] = {v.x, v.y, v.z, v.w};
+                    for (int u = 0; u < 4; ++u)
+                        if (L::pos_valid(4 * ci + u)) {
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if (L::pos_valid(4 * ci + u)) {
+                            for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
+                        }
+                }
 #pragma unroll
-                        for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
-                    }
+                for (int ci = 0; ci < HALFP / 4; ++ci) {
+                    const float4 v = mainh[ci];
+                    const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (4 * ci + u < HALFU) {
+#pragma unroll
+                            for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][VS + 4 * ci + u], e[u], acc[i]);
+                        }
+                }
+            } else {
+                const float4* x4 = reinterpret_cast<const float4*>(x + b * VS);
+#pragma unroll
+                for (int ci = 0; ci < 3 * VS / 4; ++ci) {
+                    const float4 v = x4[ci];
+                    const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if ((4 * ci + u) % VS < S) {
+#pragma unroll
+                            for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
+                        }
+                }
             }
+            scatter(acc, out);
+        };
+        // off-diagonal blocks only: O x = S_left x_{b-1} + S_right x_{b+1}
+        auto apply_O = [&](const float* x, float (&out)[OWN]) {
+            float acc[R];
+#pragma unroll
+            for (int i = 0; i < R; ++i) acc[i] = 0.f;
+            if (H == 2) {
+                const float4* side = reinterpret_cast<const float4*>(x + (b + 2 * h) * VS);
+#pragma unroll
+                for (int ci = 0; ci < VS / 4; ++ci) {
+                    const float4 v = side[ci];
+                    const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (L::pos_valid(4 * ci + u)) {
+#pragma unroll
+                            for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
+                        }
+                }
+            } else {
+                const float4* xl = reinterpret_cast<const float4*>(x + b * VS);
+                const float4* xr4 = reinterpret_cast<const float4*>(x + (b + 2) * VS);
+#pragma unroll
+                for (int ci = 0; ci < VS / 4; ++ci) {
+                    const float4 v = xl[ci], w = xr4[ci];
+                    const float e[4] = {v.x, v.y, v.z, v.w}, f[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (4 * ci + u < S) {
+#pragma unroll
+                            for (int i = 0; i < R; ++i) {
+                                acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
+                                acc[i] = fmaf(Sm[i][2 * VS + 4 * ci + u], f[u], acc[i]);
+                            }
+                        }
+                }
+            }
+            scatter(acc, out);
+        };
+        // theta_b^-1 against this knot's slot xk (no halo)
+        auto apply_T = [&](const float* xk, float (&out)[OWN]) {
+            float acc[R];
+#pragma unroll
+            for (int i = 0; i < R; ++i) acc[i] = 0.f;
+            const float4* x4 = reinterpret_cast<const float4*>(xk + h * HALFP);
 #pragma unroll
             for (int ci = 0; ci < HALFP / 4; ++ci) {
-                const float4 v = mainh[ci];
+                const float4 v = x4[ci];
                 const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
                     if (4 * ci + u < HALFU) {
 #pragma unroll
-                        for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][VS + 4 * ci + u], e[u], acc[i]);
+                        for (int i = 0; i < R; ++i) acc[i] = fmaf(Tm[i][4 * ci + u], e[u], acc[i]);
                     }
             }
-        } else {
-            const float4* x4 = reinterpret_cast<const float4*>(x + b * VS);
+            scatter(acc, out);
+        };
+        float* xr_k = xr + b * VS;
+        float* xz_k = xz + b * VS;
+        float* xt_k = xt + (b + 1) * VS;
+        float* xp_k = xp + (b + 1) * VS;
+        // r~ = P^-1 r = theta^-1 (r - O theta^-1 r); contains one block barrier
+        auto precond = [&](const float (&r_)[OWN], float (&out)[OWN]) {
+            float t[OWN], o[OWN], z[OWN];
+            store_own(xr_k, r_);
+            __syncwarp();
+            apply_T(xr_k, t);
+            store_own(xt_k, t);
+            __syncthreads();
+            apply_O(xt, o);
 #pragma unroll
-            for (int ci = 0; ci < 3 * VS / 4; ++ci) {
-                const float4 v = x4[ci];
-                const float e[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if ((4 * ci + u) % VS < S) {
-#pragma unroll
-                        for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
-                    }
-            }
-        }
-        scatter(acc, out);
-    };
-    // off-diagonal blocks only: O x = S_left x_{b-1} + S_right x_{b+1}
-    auto apply_O = [&](const float* x, float (&out)[OWN]) {
-        float acc[R];
-#pragma unroll
-        for (int i = 0; i < R; ++i) acc[i] = 0.f;
-        if (H == 2) {
-            const float4* side = reinterpret_cast<const float4*>(x + (b + 2 * h) * VS);
-#pragma unroll
-            for (int ci = 0; ci < VS / 4; ++ci) {
-                const float4 v = side[ci];
-                const float e[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if (L::pos_valid(4 * ci + u)) {
-#pragma unroll
-                        for (int i = 0; i < R; ++i) acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
-                    }
-            }
-        } else {
-            const float4* xl = reinterpret_cast<const float4*>(x + b * VS);
-            const float4* xr4 = reinterpret_cast<const float4*>(x + (b + 2) * VS);
-#pragma unroll
-            for (int ci = 0; ci < VS / 4; ++ci) {
-                const float4 v = xl[ci], w = xr4[ci];
-                const float e[4] = {v.x, v.y, v.z, v.w}, f[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if (4 * ci + u < S) {
-#pragma unroll
-                        for (int i = 0; i < R; ++i) {
-                            acc[i] = fmaf(Sm[i][4 * ci + u], e[u], acc[i]);
-                            acc[i] = fmaf(Sm[i][2 * VS + 4 * ci + u], f[u], acc[i]);
-                        }
-                    }
-            }
-        }
-        scatter(acc, out);
-    };
-    // theta_b^-1 against this knot's slot xk (no halo)
-    auto apply_T = [&](const float* xk, float (&out)[OWN]) {
-        float acc[R];
-#pragma unroll
-        for (int i = 0; i < R; ++i) acc[i] = 0.f;
-        const float4* x4 = reinterpret_cast<const float4*>(xk + h * HALFP);
-#pragma unroll
-        for (int ci = 0; ci < HALFP / 4; ++ci) {
-            const float4 v = x4[ci];
-            const float e[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (4 * ci + u < HALFU) {
-#pragma unroll
-                    for (int i = 0; i < R; ++i) acc[i] = fmaf(Tm[i][4 * ci + u], e[u], acc[i]);
-                }
-        }
-        scatter(acc, out);
-    };
-    float* xr_k = xr + b * VS;
-    float* xz_k = xz + b * VS;
-    float* xt_k = xt + (b + 1) * VS;
-    float* xp_k = xp + (b + 1) * VS;
-    // r~ = P^-1 r = theta^-1 (r - O theta^-1 r); contains one block barrier
-    auto precond = [&](const float (&r_)[OWN], float (&out)[OWN]) {
-        float t[OWN], o[OWN], z[OWN];
-        store_own(xr_k, r_);
-        __syncwarp();
-        apply_T(xr_k, t);
-        store_own(xt_k, t);
-        __syncthreads();
-        apply_O(xt, o);
-#pragma unroll
-        for (int j = 0; j < OWN; ++j) z[j] = r_[j] - o[j];
-        store_own(xz_k, z);
-        __syncwarp();
-        apply_T(xz_k, out);
-    };
+            for (int j = 0; j < OWN; ++j) z[j] = r_[j] - o[j];
+            store_own(xz_k, z);
+            __syncwarp();
+            apply_T(xz_k, out);
+        };
 
-    stamp(p, 6);
-    // ==== 5. PCG (src/gato_pcg.cuh:270-439; reductions are order-deterministic, no atomics) =======
-    float lam[OWN], rr[OWN], pp[OWN], rt[OWN], ups[OWN];
+        stamp(p, 6);
+        // ==== 5. PCG (src/gato_pcg.cuh:270-439; reductions are order-deterministic, no atomics) =======
+        float lam[OWN], rr[OWN], pp[OWN], rt[OWN], ups[OWN];
 #pragma unroll
-    for (int j = 0; j < OWN; ++j) { lam[j] = 0.f; rr[j] = ov[j] ? gam[j] : 0.f; }
-    if (p.warm == 2) {   // opt-in true warm start: r0 = gamma - S lambda0
-        const float* l0 = p.lambda_in + (long long)sys * p.ldl;
+        for (int j = 0; j < OWN; ++j) { lam[j] = 0.f; rr[j] = ov[j] ? gam[j] : 0.f; }
+        if (p.warm == 2) {   // opt-in true warm start: r0 = gamma - S lambda0
+            const float* l0 = p.lambda_in + (long long)sys * p.ldl;
 #pragma unroll
-        for (int j = 0; j < OWN; ++j)
-            if (ov[j]) lam[j] = __ldg(l0 + b * S + orow[j]);
-        store_own(xp_k, lam);
-        __syncthreads();
-        apply_S(xp, ups);
+            for (int j = 0; j < OWN; ++j)
+                if (ov[j]) lam[j] = __ldg(l0 + b * S + orow[j]);
+            store_own(xp_k, lam);
+            __syncthreads();
+            apply_S(xp, ups);
 #pragma unroll
-        for (int j = 0; j < OWN; ++j) rr[j] = ov[j] ? gam[j] - ups[j] : 0.f;
-        __syncthreads();
-    }
-    precond(rr, rt);
-    {
-        float part = 0.f;
-#pragma unroll
-        for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], rt[j], part);
-        part = warp_sum32(part);
-        if (lane == 0) redB[warp] = part;
-    }
-#pragma unroll
-    for (int j = 0; j < OWN; ++j) pp[j] = rt[j];
-    store_own(xp_k, pp);
-    __syncthreads();
-    float eta = block_partials_sum(redB, NW4);
-    int iters = p.max_iters;
-    float eta_last = eta;
-    stamp(p, 7);
-    for (int it = 0; it < p.max_iters; ++it) {
-        apply_S(xp, ups);
-        {
-            float part = 0.f;
-#pragma unroll
-            for (int j = 0; j < OWN; ++j) part = fmaf(pp[j], ups[j], part);
-            part = warp_sum32(part);
-            if (lane == 0) redA[warp] = part;
-        }
-        __syncthreads();
-        const float v = block_partials_sum(redA, NW4);
-        const float alpha = fast_div(eta, v);
-#pragma unroll
-        for (int j = 0; j < OWN; ++j) {
-            lam[j] = fmaf(alpha, pp[j], lam[j]);
-            rr[j] = fmaf(-alpha, ups[j], rr[j]);
+            for (int j = 0; j < OWN; ++j) rr[j] = ov[j] ? gam[j] - ups[j] : 0.f;
+            __syncthreads();
         }
         precond(rr, rt);
         {
@@ -824,89 +884,130 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             part = warp_sum32(part);
             if (lane == 0) redB[warp] = part;
         }
-        __syncthreads();
-        const float eta_new = block_partials_sum(redB, NW4);
-        eta_last = eta_new;
-        if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
-        const float beta = fast_div(eta_new, eta);
 #pragma unroll
-        for (int j = 0; j < OWN; ++j) pp[j] = fmaf(beta, pp[j], rt[j]);
+        for (int j = 0; j < OWN; ++j) pp[j] = rt[j];
         store_own(xp_k, pp);
-        eta = eta_new;
         __syncthreads();
-    }
-    stamp(p, 8);
+        float eta = block_partials_sum(redB, NW4);
+        int iters = p.max_iters;
+        float eta_last = eta;
+        stamp(p, 7);
+        for (int it = 0; it < p.max_iters; ++it) {
+            apply_S(xp, ups);
+            {
+                float part = 0.f;
+#pragma unroll
+                for (int j = 0; j < OWN; ++j) part = fmaf(pp[j], ups[j], part);
+                part = warp_sum32(part);
+                if (lane == 0) redA[warp] = part;
+            }
+            __syncthreads();
+            const float v = block_partials_sum(redA, NW4);
+            const float alpha = fast_div(eta, v);
+#pragma unroll
+            for (int j = 0; j < OWN; ++j) {
+                lam[j] = fmaf(alpha, pp[j], lam[j]);
+                rr[j] = fmaf(-alpha, ups[j], rr[j]);
+            }
+            precond(rr, rt);
+            {
+                float part = 0.f;
+#pragma unroll
+                for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], rt[j], part);
+                part = warp_sum32(part);
+                if (lane == 0) redB[warp] = part;
+            }
+            __syncthreads();
+            const float eta_new = block_partials_sum(redB, NW4);
+            eta_last = eta_new;
+            if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
+            const float beta = fast_div(eta_new, eta);
+#pragma unroll
+            for (int j = 0; j < OWN; ++j) pp[j] = fmaf(beta, pp[j], rt[j]);
+            store_own(xp_k, pp);
+            eta = eta_new;
+            __syncthreads();
+        }
+        stamp(p, 8);
 
-    // ==== 6. dz = G^-1 (g - C^T lambda)  (src/gato_schur.cuh:759-867) =============================
-    store_own(xp_k, lam);
-    if (active) {
+        sys = ctl[0];   // re-read: nothing about the loop is kept in registers across the PCG loop
+        // ==== 6. dz = G^-1 (g - C^T lambda)  (src/gato_schur.cuh:759-867) =============================
+        store_own(xp_k, lam);
+        if (active) {
 #pragma unroll
-        for (int j = 0; j < OWN; ++j)
-            if (ov[j]) p.lambda_out[(long long)sys * p.ldlo + b * S + orow[j]] = lam[j];
-    }
-    __syncthreads();
-    if (active) {
-        float ln[S];                                    // lambda_{b+1}; zero past the horizon
-        load_row(xp + (b + 2) * VS, ln);
-        float tb[OWN];
-#pragma unroll
-        for (int j = 0; j < OWN; ++j) {
-            tb[j] = 0.f;
-            if (ovr[j]) {   // (A^T lambda_{b+1})[row] = sum_k A[k,row] lambda_{b+1}[k]: column `row` of A is contiguous
-                float col[S];
-                load_row(kn + L::oA + orow[j] * VS, col);
-                float acc = 0.f;
-#pragma unroll
-                for (int k = 0; k < S; ++k) acc = fmaf(col[k], ln[k], acc);
-                tb[j] = kn[L::oq + po0 + j] - (lam[j] + acc);
-            }
+            for (int j = 0; j < OWN; ++j)
+                if (ov[j]) p.lambda_out[(long long)sys * p.ldlo + b * S + orow[j]] = lam[j];
         }
-        store_own(xz_k, tb);
+        __syncthreads();
+        if (active) {
+            float ln[S];                                    // lambda_{b+1}; zero past the horizon
+            load_row(xp + (b + 2) * VS, ln);
+            float tb[OWN];
 #pragma unroll
-        for (int j = 0; j < OWNC; ++j) {
-            const int cr = MC::row(lik, j);
-            if (cr >= 0) {
-                float col[S];
-                load_row(kn + L::oB + cr * VS, col);
-                float acc = 0.f;
+            for (int j = 0; j < OWN; ++j) {
+                tb[j] = 0.f;
+                if (ovr[j]) {   // (A^T lambda_{b+1})[row] = sum_k A[k,row] lambda_{b+1}[k]: column `row` of A is contiguous
+                    float col[S];
+                    load_row(kn + L::oA + orow[j] * VS, col);
+                    float acc = 0.f;
 #pragma unroll
-                for (int k = 0; k < S; ++k) acc = fmaf(col[k], ln[k], acc);
-                xr_k[cr] = kn[L::or_ + cr] - acc;
+                    for (int k = 0; k < S; ++k) acc = fmaf(col[k], ln[k], acc);
+                    tb[j] = kn[L::oq + po0 + j] - (lam[j] + acc);
+                }
             }
-        }
-    }
-    __syncwarp();
-    if (active) {
-        float* dz = p.dz_out + (long long)sys * p.lddz + (long long)b * (S + C);
-        float tbv[S];
-        load_row(xz_k, tbv);
-#pragma unroll
-        for (int j = 0; j < OWN; ++j)
-            if (ovr[j]) {
-                float qrow[S];
-                load_row(kn + L::oQ + orow[j] * VS, qrow);
-                float acc = 0.f;
-#pragma unroll
-                for (int k = 0; k < S; ++k) acc = fmaf(qrow[k], tbv[k], acc);
-                dz[orow[j]] = acc;
-            }
-        if (b < K - 1) {
+            store_own(xz_k, tb);
 #pragma unroll
             for (int j = 0; j < OWNC; ++j) {
                 const int cr = MC::row(lik, j);
                 if (cr >= 0) {
+                    float col[S];
+                    load_row(kn + L::oB + cr * VS, col);
                     float acc = 0.f;
 #pragma unroll
-                    for (int k = 0; k < C; ++k) acc = fmaf(kn[L::oR + cr * LDC + k], xr_k[k], acc);
-                    dz[S + cr] = acc;
+                    for (int k = 0; k < S; ++k) acc = fmaf(col[k], ln[k], acc);
+                    xr_k[cr] = kn[L::or_ + cr] - acc;
                 }
             }
         }
-    }
-    stamp(p, 9);
-    if (tid == 0) {
-        p.iters_out[sys] = iters;
-        if (p.eta_out != nullptr) p.eta_out[sys] = fabsf(eta_last);
+        __syncwarp();
+        if (active) {
+            float* dz = p.dz_out + (long long)sys * p.lddz + (long long)b * (S + C);
+            float tbv[S];
+            load_row(xz_k, tbv);
+#pragma unroll
+            for (int j = 0; j < OWN; ++j)
+                if (ovr[j]) {
+                    float qrow[S];
+                    load_row(kn + L::oQ + orow[j] * VS, qrow);
+                    float acc = 0.f;
+#pragma unroll
+                    for (int k = 0; k < S; ++k) acc = fmaf(qrow[k], tbv[k], acc);
+                    dz[orow[j]] = acc;
+                }
+            if (b < K - 1) {
+#pragma unroll
+                for (int j = 0; j < OWNC; ++j) {
+                    const int cr = MC::row(lik, j);
+                    if (cr >= 0) {
+                        float acc = 0.f;
+#pragma unroll
+                        for (int k = 0; k < C; ++k) acc = fmaf(kn[L::oR + cr * LDC + k], xr_k[k], acc);
+                        dz[S + cr] = acc;
+                    }
+                }
+            }
+        }
+        stamp(p, 9);
+        if (tid == 0) {
+            p.iters_out[sys] = iters;
+            if (p.eta_out != nullptr) p.eta_out[sys] = fabsf(eta_last);
+        }
+        __syncthreads();   // dz has read the knot regions and the iterates: the next system may clear them
+        if (tid == 0) {
+            ctl[0] = sys + (int)gridDim.x;
+            ctl[1] ^= 1;
+        }
+        __syncthreads();
     }
 }
 

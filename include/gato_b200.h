@@ -79,6 +79,13 @@ int gato_plan_get_cluster(const gato_plan* plan, int* cluster_ctas, int* knots_p
 int gato_plan_set_kernel(gato_plan* plan, int kernel);
 int gato_plan_get_kernel(const gato_plan* plan);
 
+/* One-CTA kernel only: stage each system's value arrays into shared memory with TMA bulk copies
+ * (cp.async.bulk; the next system's copy overlaps the current solve in the persistent CTA) whenever the
+ * staging area fits beside the system (default on); 0 = always read them with per-thread loads.  Same
+ * results bit for bit.  Replaces the per-row scalar loads of csr_to_custom_G / csr_to_custom_C
+ * (src/gato_schur.cuh:674-743). */
+int gato_plan_set_staging(gato_plan* plan, int on);
+
 /* Chunk pipeline of gato_solve_batched: the batch is cut into chunks of `systems_per_chunk` systems
  * whose H2D copy, kernel and D2H copy run on rotating streams, so the copy of chunk i+1 overlaps the
  * solve of chunk i (the reference copies, solves and copies back strictly in sequence on stream 0,
