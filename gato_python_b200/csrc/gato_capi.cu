@@ -203,6 +203,7 @@ int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     const bool staged = pl->staging && (size_t)(core + stage + tail) * 4 <= (size_t)pl->smem_optin;
     q.stage_off = staged ? core : 0;
     q.tail_off = core + (staged ? stage : 0);
+    q.kpc = q.p.K;
     const size_t smem = (size_t)(q.tail_off + tail) * 4;
     // persistent grid: as many CTAs as are resident at once, each walking systems i, i + grid, ...
     constexpr int kMaxDev = 64;   // the attribute is per device: cache (smem -> occupancy) per device
@@ -232,6 +233,57 @@ int launch_v2_sc(const gato_plan* pl, const gato::SolveParams2& q, cudaStream_t 
         if (nt == V2Menu<S>::nt[2]) return launch_v2_t<S, C, V2Menu<S>::nt[2]>(pl, q, st);
     }
     return fail(GATO_EUNSUPPORTED, "K=%d does not fit the one-CTA kernel", pl->K);
+}
+
+// ---- v2 over a thread-block cluster (kernel 3): horizons beyond one SM's registers ---------------------
+struct ClusterCfg { int ncta, kpc, nt; size_t smem; };
+
+template <int S, int C>
+int v2cl_cfg(const gato_plan* pl, ClusterCfg* out) {
+    using L = gato::Layout2<S, C>;
+    const int nt = V2Menu<S>::nt[V2Menu<S>::n - 1];
+    const int maxk = (nt / 32) * L::KPW - 2;            // two of a CTA's knot slots are halo knots
+    if (maxk < 1) return fail(GATO_EUNSUPPORTED, "no cluster variant for S=%d", S);
+    int ncta = (pl->K + maxk - 1) / maxk;
+    if (ncta < 2) ncta = 2;
+    if (pl->K < 2) return fail(GATO_EUNSUPPORTED, "the cluster variant of the one-CTA kernel needs K >= 2");
+    if (ncta > 16) return fail(GATO_EUNSUPPORTED, "K=%d needs %d CTAs: more than one 16-CTA cluster", pl->K, ncta);
+    const int kpc = (pl->K + ncta - 1) / ncta;
+    ncta = (pl->K + kpc - 1) / kpc;                      // no empty CTA at the end
+    const size_t smem = (size_t)(L::smem_floats_cl(kpc, nt) + 8) * 4;
+    if (smem > (size_t)pl->smem_optin)
+        return fail(GATO_EUNSUPPORTED, "cluster variant: %zu B shared memory per CTA > %d", smem, pl->smem_optin);
+    out->ncta = ncta; out->kpc = kpc; out->nt = nt; out->smem = smem;
+    return GATO_OK;
+}
+
+template <int S, int C>
+int launch_v2cl_sc(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
+    using L = gato::Layout2<S, C>;
+    constexpr int NT = V2Menu<S>::nt[V2Menu<S>::n - 1];
+    ClusterCfg cfg;
+    int rc = v2cl_cfg<S, C>(pl, &cfg);
+    if (rc) return rc;
+    auto kern = gato::gato_fused_solve_v2<S, C, NT, true>;
+    q.stage_off = 0;
+    q.tail_off = L::smem_floats_cl(cfg.kpc, NT);
+    q.kpc = cfg.kpc;
+    GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
+    if (cfg.ncta > 8) GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)(q.p.nsys * cfg.ncta), 1, 1);
+    lc.blockDim = dim3((unsigned)NT, 1, 1);
+    lc.dynamicSmemBytes = cfg.smem;
+    lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)cfg.ncta;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    lc.attrs = at;
+    lc.numAttrs = 1;
+    GATO_CUDA(cudaLaunchKernelEx(&lc, kern, q));
+    return GATO_OK;
 }
 
 template <int S, int C>
@@ -318,8 +370,28 @@ int v2_nt_for(const gato_plan* pl) {
 }
 
 bool use_v2(const gato_plan* pl) {
-    if (pl->kernel == 1 || (pl->kernel == 0 && pl->cl_override > 0)) return false;
+    if (pl->kernel == 1 || pl->kernel == 3 || (pl->kernel == 0 && pl->cl_override > 0)) return false;
     return v2_nt_for(pl) > 0;
+}
+
+int v2cl_cfg_for(const gato_plan* pl, ClusterCfg* cfg) {
+#define X(s, c) if (pl->S == s && pl->C == c) return v2cl_cfg<s, c>(pl, cfg);
+    GATO_FOR_SIZES(X)
+#undef X
+    return fail(GATO_EUNSUPPORTED, "no kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+// kernel 3 (the one-CTA kernel spread over a cluster): explicit choice, or automatic for horizons the
+// one-CTA kernel cannot hold
+bool use_v2cl(const gato_plan* pl) {
+    if (pl->kernel == 3) return true;
+    if (pl->kernel != 0 || pl->cl_override > 0 || v2_nt_for(pl) > 0) return false;
+    if (pl->S <= 8) return false;   // small states: 1024-thread CTAs make its barriers dearer than kernel 1's (measured)
+    ClusterCfg cfg;
+    const std::string keep = g_err;
+    const bool ok = v2cl_cfg_for(pl, &cfg) == GATO_OK;
+    g_err = keep;
+    return ok;
 }
 
 int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
@@ -328,6 +400,17 @@ int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v2_sc<s, c>(pl, q, st);
+    GATO_FOR_SIZES(X)
+#undef X
+    return fail(GATO_EUNSUPPORTED, "no v2 kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+int launch_solve_v2cl(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+    gato::SolveParams2 q;
+    q.p = p;
+    q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
+#define X(s, c) if (pl->S == s && pl->C == c) return launch_v2cl_sc<s, c>(pl, q, st);
     GATO_FOR_SIZES(X)
 #undef X
     return fail(GATO_EUNSUPPORTED, "no v2 kernels for S=%d C=%d", pl->S, pl->C);
@@ -344,6 +427,7 @@ void v2_maps_for(const gato_plan* pl, const std::vector<int>& gmap, const std::v
 // the kernel the plan selects; dumps of the Schur intermediates exist only in the cluster kernel
 int launch_auto(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
     if (p.dbg_S == nullptr && use_v2(pl)) return launch_solve_v2(pl, p, st);
+    if (p.dbg_S == nullptr && use_v2cl(pl)) return launch_solve_v2cl(pl, p, st);
     return launch_solve(pl, p, st);
 }
 

@@ -81,6 +81,13 @@ struct Layout2 {
         const int nkp = (nt / 32) * KPW;
         return K * KN + (2 * (nkp + 2) + 2 * nkp) * VS + 64;
     }
+    // cluster variant: kpc own knots + 2 halo knot regions per CTA, two partial arrays with one entry per
+    // warp of every CTA of a (<= 16-CTA) cluster
+    __host__ __device__ static constexpr int red_cl(int nt) { return (16 * (nt / 32) + 3) & ~3; }
+    __host__ __device__ static constexpr int smem_floats_cl(int kpc, int nt) {
+        const int nkp = (nt / 32) * KPW;
+        return (kpc + 2) * KN + (2 * (nkp + 2) + 2 * nkp) * VS + 2 * red_cl(nt);
+    }
 };
 
 // row maps for the in-register Gauss-Jordan: which lane-in-knot / register holds row r
@@ -166,6 +173,7 @@ struct SolveParams2 {
     int stage_off;        // > 0: float offset of the TMA staging area in shared memory (values of C, G and g
                           // arrive by cp.async.bulk, the NEXT system's while this one iterates); 0: direct loads
     int tail_off;         // float offset of the 32-byte control tail: mbarrier | current system | mbarrier parity
+    int kpc;              // cluster variant: knots owned per CTA (local slots 1..kpc; 0 and kpc+1 are halos)
 };
 
 // ---- TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier) ---------------------
@@ -207,7 +215,17 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // NT = threads per CTA (a multiple of 32, >= LPK * K).  The register file is split over the four SM
 // sub-partitions (16 K registers each, warps dealt round-robin), so the cap per thread is
 // 16384 / (32 * ceil(warps / 4)); __launch_bounds__ derives exactly that from NT.
-template <int S, int C, int NT>
+//
+// CL = true: the same kernel over ONE THREAD-BLOCK CLUSTER per system, for horizons that do not fit one
+// SM's registers (IIWA: K > 56).  CTA c of the cluster owns q.kpc consecutive knots as local slots
+// 1..kpc; slot 0 / slot kpc+1 are HALO knots (the last knot of CTA c-1 / the first of CTA c+1) whose lanes
+// redo just enough of the Schur phase (Q^-1, R^-1 of the left halo; phi of the right halo) that no CTA
+// ever READS a neighbour's shared memory.  During PCG the boundary knots push their slices of p and
+// theta^-1 r into the neighbour CTA's halo slot through DSMEM, every warp pushes its dot-product partial
+// to every CTA, and the four block barriers per iteration become cluster barriers
+// (barrier.cluster arrive.release / wait.acquire); all CTAs sum the same partials in the same order, so
+// they agree bit for bit on alpha, beta and the exit test.
+template <int S, int C, int NT, bool CL = false>
 __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 q) {
     using L = Layout2<S, C>;
     using MS = MapState<S, C>;
@@ -238,8 +256,14 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         if (g_.bytes) bulk_g2s(stG_, g_.src, g_.bytes, mbar);
         if (v_.bytes) bulk_g2s(stg_, v_.src, v_.bytes, mbar);
     };
+    int crank = 0, ncta = 1;
+    if constexpr (CL) {
+        cg::cluster_group cluster = cg::this_cluster();
+        crank = (int)cluster.block_rank();
+        ncta = (int)cluster.dim_blocks().x;
+    }
     if (threadIdx.x == 0) {
-        ctl[0] = blockIdx.x;
+        ctl[0] = CL ? blockIdx.x / ncta : blockIdx.x;
         ctl[1] = 0;
         if (staged) {
             mbar_init(mbar, 1);
@@ -262,20 +286,27 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 
         const int tid = (int)threadIdx.x + opaque, warp = tid >> 5, lane = tid & 31;
         const int lik = lane % LPK;                     // lane in knot
-        const int b = warp * L::KPW + lane / LPK;       // knot / block row owned by this lane group
-        const bool active = b < K;
+        const int slot = warp * L::KPW + lane / LPK;    // local knot slot of this lane group
+        const int k0 = CL ? crank * q.kpc : 0;          // first knot owned by this CTA
+        const int b = CL ? k0 - 1 + slot : slot;        // GLOBAL knot / block row of this lane group
+        const bool active = CL ? (slot >= 1 && slot <= q.kpc && b < K) : (b < K);   // owns block row b
+        const bool lhalo = CL && slot == 0 && b >= 0;           // redoes Q^-1, R^-1 of the previous CTA's last knot
+        const bool rhalo = CL && slot == q.kpc + 1 && b < K;    // redoes phi of the next CTA's first knot
+        const int nreg = CL ? q.kpc + 2 : K;            // knot regions in this CTA's shared memory
+        const int xb = CL ? slot - 1 : slot;            // iterate slot of the LEFT neighbour (own = xb + 1)
         const int h = lik % H, g = lik / H;             // column group, row group (matrix mapping)
 
         // ---- shared memory carve-up ----------------------------------------------------------------
-        float* kn = smem + (active ? b : 0) * KN;          // this knot's region
-        float* xp = smem + K * KN;                         // p  with one-knot halos  [(NKP+2) VS]
+        float* kn = smem + ((active || lhalo || rhalo) ? slot : 0) * KN;   // this knot's region
+        float* xp = smem + nreg * KN;                      // p  with one-knot halos  [(NKP+2) VS]
         float* xt = xp + (NKP + 2) * VS;                   // t  with one-knot halos  [(NKP+2) VS]
         float* xr = xt + (NKP + 2) * VS;                   // r  (own knot only)      [NKP VS]
         float* xz = xr + NKP * VS;                         // z  (own knot only)      [NKP VS]
-        float* redA = xz + NKP * VS;                       // per-warp partials of p.Sp    [32]
-        float* redB = redA + 32;                           // per-warp partials of r.P^-1r [32]
-        const int nfloats = L::smem_floats(K, NT);
-
+        constexpr int NRED = CL ? L::red_cl(NT) : 32;
+        float* redA = xz + NKP * VS;                       // per-warp partials of p.Sp    [NRED]
+        float* redB = redA + NRED;                         // per-warp partials of r.P^-1r [NRED]
+        const int nfloats = CL ? L::smem_floats_cl(q.kpc, NT) : L::smem_floats(K, NT);
+        const int nred4 = CL ? (ncta * NW + 3) / 4 : NW4;  // float4 words of partials to sum
         // rows of the iterates (and of the Schur-phase row work) owned by this lane: OWN consecutive
         // positions starting at po0
         const int po0 = L::own_valid(lik, 0) ? L::pos(L::own_row(lik, 0)) : 0;
@@ -298,8 +329,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 for (int j = 0; j < OWN; ++j) v[j] = ovr[j] ? base[po0 + j] : 0.f;
             }
         };
-        auto store_own = [&](float* base, const float (&v)[OWN]) {   // entries of invalid rows are zero
-            if (!active) return;
+        auto store_own_if = [&](bool en, float* base, const float (&v)[OWN]) {   // entries of invalid rows are zero
+            if (!en) return;
             if constexpr (VEC) {
                 *reinterpret_cast<float4*>(base + po0) = make_float4(v[0], v[1], v[2], v[OWN - 1]);
             } else {
@@ -308,13 +339,50 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                     if (ovr[j]) base[po0 + j] = v[j];
             }
         };
+        auto store_own = [&](float* base, const float (&v)[OWN]) { store_own_if(active, base, v); };
+        // every thread of the system passes here: block barrier, or cluster barrier over all its CTAs
+        auto sync_all = [&]() {
+            if constexpr (CL) cg::this_cluster().sync(); else __syncthreads();
+        };
+        // cluster variant: the boundary knots also write their slice of an iterate into the neighbour CTA's
+        // halo slot (my left neighbour's slot kpc+1 / my right neighbour's slot 0) through DSMEM
+        const bool pushL = CL && active && slot == 1 && crank > 0;
+        const bool pushR = CL && active && slot == q.kpc && b + 1 < K;
+        auto push_halo = [&](float* arr, const float (&v)[OWN]) {   // arr = xp or xt (slot 0 of the halo layout)
+            if constexpr (CL) {
+                if (pushL || pushR) {
+                    cg::cluster_group cluster = cg::this_cluster();
+#pragma unroll
+                    for (int side = 0; side < 2; ++side) {
+                        if (!(side ? pushR : pushL)) continue;
+                        float* rem = cluster.map_shared_rank(arr + (side ? 0 : q.kpc + 1) * VS, crank + (side ? 1 : -1));
+                        if constexpr (VEC) {
+                            *reinterpret_cast<float4*>(rem + po0) = make_float4(v[0], v[1], v[2], v[OWN - 1]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < OWN; ++j)
+                                if (ovr[j]) rem[po0 + j] = v[j];
+                        }
+                    }
+                }
+            }
+        };
+        // per-warp partial of a dot product -> the partial array of every CTA of the system
+        auto put_partial = [&](float* red, float part) {
+            if constexpr (CL) {
+                if (lane < ncta) cg::this_cluster().map_shared_rank(red, lane)[crank * NW + warp] = part;
+            } else {
+                if (lane == 0) red[warp] = part;
+            }
+        };
+
 
         stamp(p, 0);
         {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0
             float4* s4 = reinterpret_cast<float4*>(smem);
             for (int i = tid; i < nfloats / 4; i += NT) s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        __syncthreads();
+        sync_all();   // cluster variant: no CTA pushes into a halo slot that its owner has yet to clear
         stamp(p, 1);
 
         const float* cv = p.c + (long long)sys * p.ldc;
@@ -336,9 +404,16 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         // One CTA per SM means memory latency is hidden only by the loads each thread keeps in flight:
         // every round issues UB (map, value) pairs per thread before the first dependent store.
         {
+            // cluster variant: only the non-zeros of this CTA's knots (left halo .. last own knot); the maps hold
+            // GLOBAL knot offsets, so the local destination is the map entry minus (k0 - 1) regions
+            const int kA = CL ? max(k0 - 1, 0) : 0, kB = CL ? min(k0 + q.kpc, K) : K;   // knots [kA, kB)
+            const int cA = CL ? __ldg(p.cstart + kA) : 0, cB = CL ? __ldg(p.cstart + kB) : q.nnzC;
+            const int gA = CL ? __ldg(p.gstart + kA) : 0, gB = CL ? __ldg(p.gstart + kB) : q.nnzG;
+            const int zA = CL ? kA * (S + C) : 0, zB = CL ? min(kB * (S + C), (S + C) * K - C) : (S + C) * K - C;
+            const int shift = CL ? (k0 - 1) * KN : 0;
             constexpr int UB = 16;
 #pragma unroll 1
-            for (int t0 = tid; t0 < q.nnzC; t0 += NT * UB) {
+            for (int t0 = cA + tid; t0 < cB; t0 += NT * UB) {
                 int m[UB];
                 float v[UB];
 #pragma unroll
@@ -346,16 +421,15 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                     const int t = t0 + u * NT;
                     m[u] = -1;
                     v[u] = 0.f;
-                    if (t < q.nnzC) { m[u] = __ldg(q.cdst + t); v[u] = Cv[t]; }
+                    if (t < cB) { m[u] = __ldg(q.cdst + t); v[u] = Cv[t]; }
                 }
 #pragma unroll
                 for (int u = 0; u < UB; ++u)
-                    if (m[u] >= 0) smem[m[u]] = v[u];
+                    if (m[u] >= 0) smem[m[u] - shift] = v[u];
             }
             constexpr int UG = 8;
-            const int n_z = (S + C) * K - C;
 #pragma unroll 1
-            for (int t0 = tid; t0 < max(q.nnzG, n_z); t0 += NT * UG) {
+            for (int t0 = tid; t0 < max(gB - gA, zB - zA); t0 += NT * UG) {
                 int m[UG];
                 float v[UG], w[UG];
 #pragma unroll
@@ -363,22 +437,22 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                     const int t = t0 + u * NT;
                     m[u] = -1;
                     v[u] = w[u] = 0.f;
-                    if (t < q.nnzG) { m[u] = __ldg(q.gdst + t); v[u] = Gv[t]; }
-                    if (t < n_z) w[u] = gv[t];
+                    if (gA + t < gB) { m[u] = __ldg(q.gdst + gA + t); v[u] = Gv[gA + t]; }
+                    if (zA + t < zB) w[u] = gv[zA + t];
                 }
 #pragma unroll
                 for (int u = 0; u < UG; ++u) {
-                    const int t = t0 + u * NT;
-                    if (m[u] >= 0) smem[m[u] & kMapMask] = v[u] + ((m[u] & kMapDiagBit) ? p.rho : 0.0f);
-                    if (t < n_z) {   // g -> per-knot q (pos layout) | r
+                    const int t = zA + t0 + u * NT;
+                    if (m[u] >= 0) smem[(m[u] & kMapMask) - shift] = v[u] + ((m[u] & kMapDiagBit) ? p.rho : 0.0f);
+                    if (t < zB) {   // g -> per-knot q (pos layout) | r
                         const int k = t / (S + C), o = t - k * (S + C);
-                        smem[k * KN + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = w[u];
+                        smem[k * KN - shift + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = w[u];
                     }
                 }
             }
         }
         __syncthreads();
-        if (staged && tid == 0 && sys + (int)gridDim.x < p.nsys) {
+        if (!CL && staged && tid == 0 && sys + (int)gridDim.x < p.nsys) {
             // the staging area has been consumed (barrier above): fetch the next system's values now, so
             // they arrive while this system iterates.  Generic-proxy reads -> async-proxy writes.
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -451,10 +525,12 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         }
 #pragma unroll 1
         for (int pass = 0; pass < 2; ++pass) {
+            // lanes with nothing to invert in this pass carry an identity through the warp-wide elimination
+            const bool inv = pass == 0 ? (active || lhalo) : active;
 #pragma unroll
             for (int i = 0; i < OWN; ++i)
 #pragma unroll
-                for (int j = 0; j < S; ++j) a[i][j] = (!active && MS::row(lik, i) == j) ? 1.f : 0.f;
+                for (int j = 0; j < S; ++j) a[i][j] = (!inv && MS::row(lik, i) == j) ? 1.f : 0.f;
             if (pass == 0) {
                 if (active && b == 0) {   // block row 0 keeps raw Q0 as theta_0^-1 (src/gato_schur.cuh:75-81): stash it
 #pragma unroll
@@ -467,7 +543,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                         }
                 }
                 if (q.g_diag) {   // diagonal cost blocks: the inverses are reciprocals (same bits as the elimination)
-                    if (active) {
+                    if (inv) {
 #pragma unroll
                         for (int i = 0; i < OWN; ++i)
                             if (ovr[i]) {
@@ -489,12 +565,12 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                     stamp(p, 3);
                     continue;
                 }
-                if (active) {
+                if (inv) {
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
                         if (ovr[i]) load_row(kn + L::oQ + orow[i] * VS, a[i]);
                 }
-            } else if (active) {
+            } else if (active || rhalo) {
                 if (b == 0) {
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
@@ -543,9 +619,9 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                         float col[OWN];
 #pragma unroll
                         for (int i = 0; i < OWN; ++i) col[i] = phi[i][c];
-                        store_own(kn + L::oPhi + c * VS, col);
+                        store_own_if(true, kn + L::oPhi + c * VS, col);
                     }
-                    {
+                    if (active) {   // a right-halo knot stops here: only its phi is needed (S_right of the last own knot)
                         float qv[S], qp[S];
                         load_row(kn + L::oq, qv);
                         load_row(prev + L::oq, qp);
@@ -566,23 +642,25 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                                 gam[i] = (a0 - __ldg(cv + b * S + orow[i])) + (a2 + a1);
                             }
                     }
-                    rank1_S(a, kn + L::oPhi, prev + L::oA, S);             // phi A^T
+                    if (active) rank1_S(a, kn + L::oPhi, prev + L::oA, S);   // phi A^T
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
-                        if (ovr[i]) {
+                        if (active && ovr[i]) {
                             float qrow[S];
                             load_row(kn + L::oQ + orow[i] * VS, qrow);
 #pragma unroll
                             for (int c = 0; c < S; ++c) a[i][c] += qrow[c];   // + Q_b^-1
                         }
+                    if (active) {
 #pragma unroll
-                    for (int k = 0; k < C; ++k) {                          // + BR B^T
-                        float yv[S];
-                        load_row(prev + L::oB + k * VS, yv);
+                        for (int k = 0; k < C; ++k) {                          // + BR B^T
+                            float yv[S];
+                            load_row(prev + L::oB + k * VS, yv);
 #pragma unroll
-                        for (int i = 0; i < OWN; ++i)
+                            for (int i = 0; i < OWN; ++i)
 #pragma unroll
-                            for (int c = 0; c < S; ++c) a[i][c] = fmaf(br[i][k], yv[c], a[i][c]);
+                                for (int c = 0; c < S; ++c) a[i][c] = fmaf(br[i][k], yv[c], a[i][c]);
+                        }
                     }
                 }
 #pragma unroll
@@ -592,12 +670,12 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             }
             gj_invert_knot<MS, LPK>(a, lik, lane);
             if (pass == 0) {
-                if (active) {
+                if (inv) {
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
                         if (ovr[i]) store_row(kn + L::oQ + orow[i] * VS, a[i]);
                 }
-                const bool hasR = active && b < K - 1;
+                const bool hasR = inv && b < K - 1;
                 float c2[OWNC][C];
 #pragma unroll
                 for (int i = 0; i < OWNC; ++i) {
@@ -742,8 +820,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
             for (int i = 0; i < R; ++i) acc[i] = 0.f;
             if (H == 2) {
-                const float4* side = reinterpret_cast<const float4*>(x + (b + 2 * h) * VS);
-                const float4* mainh = reinterpret_cast<const float4*>(x + (b + 1) * VS + h * HALFP);
+                const float4* side = reinterpret_cast<const float4*>(x + (xb + 2 * h) * VS);
+                const float4* mainh = reinterpret_cast<const float4*>(x + (xb + 1) * VS + h * HALFP);
 #pragma unroll
                 for (int ci = 0; ci < VS / 4; ++ci) {
                     const float4 v = side[ci];
@@ -767,7 +845,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                         }
                 }
             } else {
-                const float4* x4 = reinterpret_cast<const float4*>(x + b * VS);
+                const float4* x4 = reinterpret_cast<const float4*>(x + xb * VS);
 #pragma unroll
                 for (int ci = 0; ci < 3 * VS / 4; ++ci) {
                     const float4 v = x4[ci];
@@ -788,7 +866,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
             for (int i = 0; i < R; ++i) acc[i] = 0.f;
             if (H == 2) {
-                const float4* side = reinterpret_cast<const float4*>(x + (b + 2 * h) * VS);
+                const float4* side = reinterpret_cast<const float4*>(x + (xb + 2 * h) * VS);
 #pragma unroll
                 for (int ci = 0; ci < VS / 4; ++ci) {
                     const float4 v = side[ci];
@@ -801,8 +879,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                         }
                 }
             } else {
-                const float4* xl = reinterpret_cast<const float4*>(x + b * VS);
-                const float4* xr4 = reinterpret_cast<const float4*>(x + (b + 2) * VS);
+                const float4* xl = reinterpret_cast<const float4*>(x + xb * VS);
+                const float4* xr4 = reinterpret_cast<const float4*>(x + (xb + 2) * VS);
 #pragma unroll
                 for (int ci = 0; ci < VS / 4; ++ci) {
                     const float4 v = xl[ci], w = xr4[ci];
@@ -839,10 +917,10 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             }
             scatter(acc, out);
         };
-        float* xr_k = xr + b * VS;
-        float* xz_k = xz + b * VS;
-        float* xt_k = xt + (b + 1) * VS;
-        float* xp_k = xp + (b + 1) * VS;
+        float* xr_k = xr + slot * VS;
+        float* xz_k = xz + slot * VS;
+        float* xt_k = xt + (xb + 1) * VS;
+        float* xp_k = xp + (xb + 1) * VS;
         // r~ = P^-1 r = theta^-1 (r - O theta^-1 r); contains one block barrier
         auto precond = [&](const float (&r_)[OWN], float (&out)[OWN]) {
             float t[OWN], o[OWN], z[OWN];
@@ -850,7 +928,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             __syncwarp();
             apply_T(xr_k, t);
             store_own(xt_k, t);
-            __syncthreads();
+            push_halo(xt, t);
+            sync_all();
             apply_O(xt, o);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) z[j] = r_[j] - o[j];
@@ -870,11 +949,12 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             for (int j = 0; j < OWN; ++j)
                 if (ov[j]) lam[j] = __ldg(l0 + b * S + orow[j]);
             store_own(xp_k, lam);
-            __syncthreads();
+            push_halo(xp, lam);
+            sync_all();
             apply_S(xp, ups);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) rr[j] = ov[j] ? gam[j] - ups[j] : 0.f;
-            __syncthreads();
+            sync_all();
         }
         precond(rr, rt);
         {
@@ -882,13 +962,14 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
             for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], rt[j], part);
             part = warp_sum32(part);
-            if (lane == 0) redB[warp] = part;
+            put_partial(redB, part);
         }
 #pragma unroll
         for (int j = 0; j < OWN; ++j) pp[j] = rt[j];
         store_own(xp_k, pp);
-        __syncthreads();
-        float eta = block_partials_sum(redB, NW4);
+        push_halo(xp, pp);
+        sync_all();
+        float eta = block_partials_sum(redB, nred4);
         int iters = p.max_iters;
         float eta_last = eta;
         stamp(p, 7);
@@ -899,10 +980,10 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
                 for (int j = 0; j < OWN; ++j) part = fmaf(pp[j], ups[j], part);
                 part = warp_sum32(part);
-                if (lane == 0) redA[warp] = part;
+                put_partial(redA, part);
             }
-            __syncthreads();
-            const float v = block_partials_sum(redA, NW4);
+            sync_all();
+            const float v = block_partials_sum(redA, nred4);
             const float alpha = fast_div(eta, v);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) {
@@ -915,33 +996,35 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
                 for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], rt[j], part);
                 part = warp_sum32(part);
-                if (lane == 0) redB[warp] = part;
+                put_partial(redB, part);
             }
-            __syncthreads();
-            const float eta_new = block_partials_sum(redB, NW4);
+            sync_all();
+            const float eta_new = block_partials_sum(redB, nred4);
             eta_last = eta_new;
             if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
             const float beta = fast_div(eta_new, eta);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) pp[j] = fmaf(beta, pp[j], rt[j]);
             store_own(xp_k, pp);
+            push_halo(xp, pp);
             eta = eta_new;
-            __syncthreads();
+            sync_all();
         }
         stamp(p, 8);
 
         sys = ctl[0];   // re-read: nothing about the loop is kept in registers across the PCG loop
         // ==== 6. dz = G^-1 (g - C^T lambda)  (src/gato_schur.cuh:759-867) =============================
         store_own(xp_k, lam);
+        push_halo(xp, lam);
         if (active) {
 #pragma unroll
             for (int j = 0; j < OWN; ++j)
                 if (ov[j]) p.lambda_out[(long long)sys * p.ldlo + b * S + orow[j]] = lam[j];
         }
-        __syncthreads();
+        sync_all();
         if (active) {
             float ln[S];                                    // lambda_{b+1}; zero past the horizon
-            load_row(xp + (b + 2) * VS, ln);
+            load_row(xp + (xb + 2) * VS, ln);
             float tb[OWN];
 #pragma unroll
             for (int j = 0; j < OWN; ++j) {
@@ -998,13 +1081,13 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             }
         }
         stamp(p, 9);
-        if (tid == 0) {
+        if (tid == 0 && crank == 0) {
             p.iters_out[sys] = iters;
             if (p.eta_out != nullptr) p.eta_out[sys] = fabsf(eta_last);
         }
         __syncthreads();   // dz has read the knot regions and the iterates: the next system may clear them
         if (tid == 0) {
-            ctl[0] = sys + (int)gridDim.x;
+            ctl[0] = sys + (int)gridDim.x / ncta;
             ctl[1] ^= 1;
         }
         __syncthreads();

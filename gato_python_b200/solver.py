@@ -155,7 +155,7 @@ class Plan:
         _check(lib().gato_plan_set_cluster(self._h, int(cluster_ctas)))
 
     def set_kernel(self, kernel):
-        """0 = automatic, 1 = cluster kernel, 2 = one-CTA-per-system kernel."""
+        """0 = automatic, 1 = warp-per-knot cluster kernel, 2 = one-CTA-per-system kernel, 3 = one-CTA kernel over a cluster."""
         _check(lib().gato_plan_set_kernel(self._h, int(kernel)))
 
     def kernel(self):

@@ -71,11 +71,14 @@ void gato_plan_destroy(gato_plan* plan);
 int gato_plan_set_cluster(gato_plan* plan, int cluster_ctas);
 int gato_plan_get_cluster(const gato_plan* plan, int* cluster_ctas, int* knots_per_cta);
 
-/* Kernel selection for tuning and tests: 0 = automatic, 1 = cluster kernel (one thread-block cluster
- * per system, DSMEM exchange; any K up to 16 CTAs x 32 knots), 2 = one-CTA-per-system kernel (whole
- * system resident in one SM's registers, block barriers only; the batched path and the default
- * whenever K fits).  Both replace the same reference functions (parallelPCG, src/gato_pcg.cuh:441-470,
- * and the three Schur/dz kernels, src/gato_schur.cuh:462-494, 652-670, 869-879). */
+/* Kernel selection for tuning and tests: 0 = automatic, 1 = warp-per-knot cluster kernel (one thread-block
+ * cluster per system, DSMEM exchange; any K up to 16 CTAs x 32 knots), 2 = one-CTA-per-system kernel (whole
+ * system resident in one SM's registers, block barriers only; the batched path and the default whenever K
+ * fits), 3 = the one-CTA kernel spread over a thread-block cluster (each CTA owns a run of knots plus two
+ * halo knots; neighbour slices and dot-product partials pushed through DSMEM, cluster barriers; the default
+ * for IIWA-sized states once K exceeds one SM, e.g. K = 256 -> 5 CTAs x 52 knots).  All replace the same
+ * reference functions (parallelPCG, src/gato_pcg.cuh:441-470, and the three Schur/dz kernels,
+ * src/gato_schur.cuh:462-494, 652-670, 869-879). */
 int gato_plan_set_kernel(gato_plan* plan, int kernel);
 int gato_plan_get_kernel(const gato_plan* plan);
 

@@ -82,7 +82,7 @@ def test_unpack_bit_exact(name):
     pl.close()
 
 
-@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+@pytest.mark.parametrize("kernel", [1, 2, 3], ids=["cluster", "onecta", "onecta_cluster"])
 @pytest.mark.parametrize("name", list(CASES))
 def test_solve_vs_oracle(name, kernel):
     prob = CASES[name]()
@@ -90,8 +90,9 @@ def test_solve_vs_oracle(name, kernel):
     try:
         pl.set_kernel(kernel)
     except solver.GatoError:
-        assert kernel == 2 and name in ("iiwa256", "S4_K512_max_cluster")   # beyond one CTA: cluster kernel only
-        pytest.skip("K does not fit the one-CTA kernel")
+        # beyond one CTA: cluster kernels only; the cluster form of the one-CTA kernel needs two knots
+        assert (kernel == 2 and name in ("iiwa256", "S4_K512_max_cluster")) or (kernel == 3 and name == "ragged_K1")
+        pytest.skip("K does not fit this kernel")
     assert pl.kernel() == kernel
     warm = WARM_REFERENCE if "warmflag" in name else 0
     lam_in = np.full(prob["S"] * prob["K"], 3.0, np.float32) if warm else None
@@ -208,7 +209,7 @@ def test_edge_cases(kernel):
 
 
 def test_default_kernel_selection():
-    """K that fits one CTA runs the one-CTA kernel; longer horizons fall back to the cluster kernel."""
+    """K that fits one CTA runs the one-CTA kernel; longer horizons run over a thread-block cluster."""
     pl = plan_of(CASES["iiwa50_s0"]())
     assert pl.kernel() == 2 and pl.cluster() == (1, 50)
     pl.set_cluster(8)
@@ -216,7 +217,10 @@ def test_default_kernel_selection():
     pl.set_cluster(0)
     assert pl.kernel() == 2
     pl.close()
-    pl = plan_of(CASES["iiwa256"]())
+    pl = plan_of(CASES["iiwa256"]())          # IIWA horizons beyond one SM: the one-CTA kernel over a cluster
+    assert pl.kernel() == 3 and pl.cluster() == (5, 52)
+    pl.close()
+    pl = plan_of(CASES["S4_K512_max_cluster"]())   # small states: the warp-per-knot cluster kernel
     assert pl.kernel() == 1
     pl.close()
 
