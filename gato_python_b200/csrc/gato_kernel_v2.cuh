@@ -86,7 +86,7 @@ struct Layout2 {
     __host__ __device__ static constexpr int red_cl(int nt) { return (16 * (nt / 32) + 3) & ~3; }
     __host__ __device__ static constexpr int smem_floats_cl(int kpc, int nt) {
         const int nkp = (nt / 32) * KPW;
-        return (kpc + 2) * KN + (2 * (nkp + 2) + 2 * nkp) * VS + 2 * red_cl(nt);
+        return (kpc + 2) * KN + (2 * (nkp + 2) + 2 * nkp) * VS + 2 * red_cl(nt) + 2 * VS;
     }
 };
 
@@ -305,6 +305,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         constexpr int NRED = CL ? L::red_cl(NT) : 32;
         float* redA = xz + NKP * VS;                       // per-warp partials of p.Sp    [NRED]
         float* redB = redA + NRED;                         // per-warp partials of r.P^-1r [NRED]
+        float* xq = redB + NRED;                           // cluster variant: r~ of the two knots across the CTA
+                                                           // boundaries, [0] left, [1] right  [2 VS]
         const int nfloats = CL ? L::smem_floats_cl(q.kpc, NT) : L::smem_floats(K, NT);
         const int nred4 = CL ? (ncta * NW + 3) / 4 : NW4;  // float4 words of partials to sum
         // rows of the iterates (and of the Schur-phase row work) owned by this lane: OWN consecutive
@@ -991,6 +993,25 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 rr[j] = fmaf(-alpha, ups[j], rr[j]);
             }
             precond(rr, rt);
+            if constexpr (CL) {
+                // r~ of the boundary knots travels with the reduction's barrier: the neighbour CTA then forms
+                // p_new of its halo knot itself (same fmaf, same bits) and the p exchange needs no cluster barrier
+                if (pushL || pushR) {
+                    cg::cluster_group cluster = cg::this_cluster();
+#pragma unroll
+                    for (int side = 0; side < 2; ++side) {
+                        if (!(side ? pushR : pushL)) continue;
+                        float* rem = cluster.map_shared_rank(xq + (side ? 0 : VS), crank + (side ? 1 : -1));
+                        if constexpr (VEC) {
+                            *reinterpret_cast<float4*>(rem + po0) = make_float4(rt[0], rt[1], rt[2], rt[OWN - 1]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < OWN; ++j)
+                                if (ovr[j]) rem[po0 + j] = rt[j];
+                        }
+                    }
+                }
+            }
             {
                 float part = 0.f;
 #pragma unroll
@@ -1006,9 +1027,21 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
             for (int j = 0; j < OWN; ++j) pp[j] = fmaf(beta, pp[j], rt[j]);
             store_own(xp_k, pp);
-            push_halo(xp, pp);
             eta = eta_new;
-            sync_all();
+            if constexpr (CL) {
+#pragma unroll
+                for (int side = 0; side < 2; ++side) {
+                    if (!(side ? pushR : pushL)) continue;
+                    float* ph = xp + (side ? slot + 1 : 0) * VS;      // halo slot holding the neighbour's p
+                    const float* qh = xq + (side ? VS : 0);           // its r~, pushed before the barrier above
+#pragma unroll
+                    for (int j = 0; j < OWN; ++j)
+                        if (VEC || ovr[j]) ph[po0 + j] = fmaf(beta, ph[po0 + j], qh[po0 + j]);
+                }
+                __syncthreads();
+            } else {
+                sync_all();
+            }
         }
         stamp(p, 8);
 
