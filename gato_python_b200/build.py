@@ -38,7 +38,7 @@ def _stale(target, sources):
 
 def _lib_sources():
     srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))
-            if f.endswith((".cu", ".cuh", ".inc", ".h"))]
+            if f.endswith((".cu", ".cuh", ".inc", ".h")) and f not in ("floors.cu", "gpu_library.cu")]
     srcs.append(os.path.join(ROOT, "include", "gato_b200.h"))
     return srcs
 
@@ -85,11 +85,22 @@ def build_module(S, C, K, force=False):
     return out_dir
 
 
+def build_floors(force=False):
+    """build/floors: micro-benchmarks of the launch / barrier floors (csrc/floors.cu)."""
+    src = os.path.join(CSRC, "floors.cu")
+    out = os.path.join(ROOT, "build", "floors")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    if force or _stale(out, [src]):
+        subprocess.run([_nvcc()] + ARCH + ["-O3", "-std=c++17", "-lineinfo", "-rdc=true", src, "-o", out], check=True)
+    return out
+
+
 DEFAULT_MODULES = [(2, 1, 5), (14, 7, 50), (14, 7, 256)]
 
 
 def build_all(force=False):
     build_library(force=force)
+    build_floors(force=force)
     return [build_module(S, C, K, force=force) for (S, C, K) in DEFAULT_MODULES]
 
 
