@@ -43,3 +43,50 @@ def solve_sharded(solve_fn, nsys, arrays, group=None, dst=0):
     assert parts[0][0] == 0 and parts[-1][1] == nsys and all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
     return (np.concatenate([p[2] for p in parts]), np.concatenate([p[3] for p in parts]),
             np.concatenate([p[4] for p in parts]))
+
+
+# ------------------------------------------------------------------------------------------------
+# Host placement: one process per GPU should run, and pin its staging memory, on the GPU's own NUMA node
+# ------------------------------------------------------------------------------------------------
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        a, _, b = part.partition("-")
+        cpus.update(range(int(a), int(b or a) + 1))
+    return cpus
+
+
+def gpu_numa_node(index: int):
+    """NUMA node of CUDA device `index` from its PCI address (sysfs), or None when unknown."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.lower().split(":", 1)
+        with open(f"/sys/bus/pci/devices/{dom[-4:]}:{rest}/numa_node") as f:
+            node = int(f.read().strip())
+        return node if node >= 0 else None
+    except Exception:
+        return None
+
+
+def bind_to_gpu_numa(index: int):
+    """Restrict this process to the CPUs of GPU `index`'s NUMA node, so that the pinned host buffers it
+    allocates afterwards are first-touched there and its H2D/D2H copies do not cross the socket link.
+    Returns {"node", "cpus"} or None when the topology is unknown (nothing is changed then)."""
+    import os
+    node = gpu_numa_node(index)
+    if node is None:
+        return None
+    try:
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = _parse_cpulist(f.read()) & os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"node": node, "cpus": len(cpus)}
+    except Exception:
+        return None
