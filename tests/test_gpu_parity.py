@@ -175,7 +175,7 @@ def test_cluster_shapes_agree(cl):
     pl.close()
 
 
-@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+@pytest.mark.parametrize("kernel", [1, 2, 3], ids=["cluster", "onecta", "onecta_cluster"])
 def test_true_warm_start_extension(kernel):
     prob = CASES["iiwa50_s0"]()
     pl = plan_of(prob)
@@ -190,7 +190,7 @@ def test_true_warm_start_extension(kernel):
     pl.close()
 
 
-@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+@pytest.mark.parametrize("kernel", [1, 2, 3], ids=["cluster", "onecta", "onecta_cluster"])
 def test_edge_cases(kernel):
     prob = CASES["iiwa50_s0"]()
     pl = plan_of(prob)
@@ -225,7 +225,7 @@ def test_default_kernel_selection():
     pl.close()
 
 
-@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+@pytest.mark.parametrize("kernel", [1, 2, 3], ids=["cluster", "onecta", "onecta_cluster"])
 def test_batched_matches_single_and_oracle(kernel):
     b = iiwa_like_batch(24, K=50, seed0=1000)
     pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"])
@@ -395,7 +395,7 @@ def _mpc_inputs(prob, nsteps, seed=0):
     return g, c, rho
 
 
-@pytest.mark.parametrize("kernel", [1, 2], ids=["cluster", "onecta"])
+@pytest.mark.parametrize("kernel", [1, 2, 3], ids=["cluster", "onecta", "onecta_cluster"])
 def test_sequence_api_matches_step_by_step(kernel):
     """gato_solve_sequence == the same solves issued one by one (bitwise), in the reference-faithful
     mode and with the true warm start; the warm chain equals GATO_WARM_RESIDENT and the oracle."""
@@ -493,3 +493,38 @@ def test_dropin_module_extensions():
     for t in range(T):   # blocks: c shared (row 0), rho fixed
         lam_o, dz_o, io = oracle(dict(prob, g=g[t], c=c[0], rho=1e-3))
         assert close(o["lb"][t], lam_o) and close(o["dzb"][t], dz_o) and abs(int(o["itb"][t]) - io["iters"]) <= 1
+
+
+def test_tma_staging_is_bitwise_equal():
+    """One-CTA kernel: values staged by TMA bulk copies (persistent CTAs, next system prefetched) vs per-thread
+    loads: same bits; odd batch sizes exercise CTAs with different numbers of systems and unaligned rows."""
+    for nsys, K in ((1, 50), (149, 50), (311, 12)):
+        b = iiwa_like_batch(min(nsys, 8), K=K, seed0=70)
+        reps = (nsys + 7) // 8
+        tile = lambda a: np.ascontiguousarray(np.tile(a, (reps, 1))[:nsys])   # noqa: E731
+        G, Cv, g, c = tile(b["G_val"]), tile(b["C_val"]), tile(b["g"]), tile(b["c"])
+        g = (g * (1 + 0.01 * np.arange(nsys, dtype=np.float32)[:, None] / nsys)).astype(np.float32)
+        pl = Plan(14, 7, K, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=nsys)
+        out = {}
+        for on in (1, 0):
+            pl.set_staging(on)
+            out[on] = pl.solve_batched(G, Cv, g, c, None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+        for a, bb in zip(out[0][:3], out[1][:3]):
+            assert np.array_equal(a, bb)
+        pl.close()
+
+
+def test_cluster_form_matches_one_cta_kernel():
+    """Kernel 3 is kernel 2's code over a cluster: on a horizon both can hold they agree to rounding of the
+    reduction order (different partial grouping), iteration counts equal."""
+    b = iiwa_like_batch(16, K=50, seed0=1000)
+    pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=16)
+    res = {}
+    for kern in (2, 3):
+        pl.set_kernel(kern)
+        res[kern] = pl.solve_batched(b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0,
+                                     b["rho"])
+    assert np.abs(res[2][2] - res[3][2]).max() <= 1
+    for i in range(16):
+        assert close(res[3][0][i], res[2][0][i]) and close(res[3][1][i], res[2][1][i])
+    pl.close()

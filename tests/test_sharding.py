@@ -79,3 +79,14 @@ def test_gloo_world2_shard_and_gather():
         lo, do, io = orc.linsys_solve_info(4, 2, 6, b["G_row"], b["G_col"], b["G_val"][i], b["C_row"], b["C_col"],
                                            b["C_val"][i], b["g"][i], b["c"][i], np.zeros(24), 1, 1e-6, 100, False, 1e-3)
         assert np.array_equal(lam[i], lo) and np.array_equal(dz[i], do) and iters[i] == io["iters"]
+
+
+def test_numa_binding_helpers():
+    from gato_python_b200.sharding import _parse_cpulist, bind_to_gpu_numa
+    assert _parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert _parse_cpulist("") == set()
+    import os
+    before = os.sched_getaffinity(0)
+    r = bind_to_gpu_numa(0)          # no GPU / unknown topology: nothing changes
+    assert r is None or (r["cpus"] >= 1 and os.sched_getaffinity(0) <= before)
+    os.sched_setaffinity(0, before)
