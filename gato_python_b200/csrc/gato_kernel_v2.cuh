@@ -138,7 +138,9 @@ __device__ __forceinline__ void gj_invert_knot(float (&a)[M::N][M::D], int lik, 
         float prow[D];
 #pragma unroll
         for (int j = 0; j < D; ++j) prow[j] = __shfl_sync(0xffffffffu, a[M::reg(pv)][j], base + M::lik(pv));
-        const float inv = 1.0f / prow[pv];
+        float inv;   // reciprocal seed + one Newton step (the IEEE division subroutine sits on the pivot chain)
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(prow[pv]));
+        inv = fmaf(fmaf(-prow[pv], inv, 1.0f), inv, inv);
 #pragma unroll
         for (int i = 0; i < N; ++i) {
             if (M::row(lik, i) == pv) {
@@ -486,7 +488,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         // out[i][c] += sum_k X[row_i, k] * Y[c, k]:  X = [k][VS] with rows in pos layout (own rows are
         // one aligned load), Y = [k][VS] with its first index in pos layout (a whole column per k)
         auto rank1_S = [&](float (&out)[OWN][S], const float* X, const float* Y, int nk) {
-#pragma unroll 1
+#pragma unroll 2
             for (int k = 0; k < nk; ++k) {
                 float xv[OWN], yv[S];
                 load_own(X + k * VS, xv);
