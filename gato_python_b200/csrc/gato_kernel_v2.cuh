@@ -382,9 +382,13 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 
 
         stamp(p, 0);
-        {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0
+        {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0.
+            // A persistent CTA's later systems with a purely diagonal G write exactly the words its first system
+            // wrote in the knot regions (same pattern, reciprocals in place): only the iterates need clearing.
+            const bool keep_regions = !CL && q.g_diag && sys >= (int)gridDim.x;
             float4* s4 = reinterpret_cast<float4*>(smem);
-            for (int i = tid; i < nfloats / 4; i += NT) s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = (keep_regions ? nreg * KN / 4 : 0) + tid; i < nfloats / 4; i += NT)
+                s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         sync_all();   // cluster variant: no CTA pushes into a halo slot that its owner has yet to clear
         stamp(p, 1);
