@@ -83,6 +83,7 @@ struct gato_plan {
     int sm_count = 0;
     int smem_optin = 0;
     int staging = 1;        // v2: TMA staging of the value arrays when it fits (gato_plan_set_staging)
+    int zero_copy = 1;      // gato_solve: staged kernels read the pinned input buffer in place (gato_plan_set_zero_copy)
     int lam_slot = 0;       // gato_solve ping-pongs its output between two slots of dlo ...
     bool have_lambda = false;   // ... so the previous lambda stays readable for GATO_WARM_RESIDENT
     // device: pattern maps
@@ -392,6 +393,24 @@ bool use_v2cl(const gato_plan* pl) {
     const bool ok = v2cl_cfg_for(pl, &cfg) == GATO_OK;
     g_err = keep;
     return ok;
+}
+
+// does the one-CTA kernel run with TMA staging for this plan?
+template <int S, int C>
+bool v2_stages_sc(const gato_plan* pl) {
+    using L = gato::Layout2<S, C>;
+    const int nt = v2_pick_nt<S, C>(pl);
+    if (nt == 0 || !pl->staging) return false;
+    const int stage = gato::stage_len(pl->nnzC) + gato::stage_len(pl->nnzG) + gato::stage_len(pl->n_z);
+    return (size_t)(L::smem_floats(pl->K, nt) + stage + 8) * 4 <= (size_t)pl->smem_optin;
+}
+
+bool v2_stages(const gato_plan* pl) {
+    if (!use_v2(pl)) return false;
+#define X(s, c) if (pl->S == s && pl->C == c) return v2_stages_sc<s, c>(pl);
+    GATO_FOR_SIZES(X)
+#undef X
+    return false;
 }
 
 int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {

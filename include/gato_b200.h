@@ -89,6 +89,11 @@ int gato_plan_get_kernel(const gato_plan* plan);
  * (src/gato_schur.cuh:674-743). */
 int gato_plan_set_staging(gato_plan* plan, int on);
 
+/* gato_solve only: when the kernel stages its inputs with TMA, let those bulk copies read the plan's pinned
+ * host staging buffer in place over PCIe instead of copying it to the device first (default on).  Removes
+ * one of the two DMA operations of the reference's bracket (the H2D of gpu_library.cu:150-157).  Same results. */
+int gato_plan_set_zero_copy(gato_plan* plan, int on);
+
 /* Chunk pipeline of gato_solve_batched: the batch is cut into chunks of `systems_per_chunk` systems
  * whose H2D copy, kernel and D2H copy run on rotating streams, so the copy of chunk i+1 overlaps the
  * solve of chunk i (the reference copies, solves and copies back strictly in sequence on stream 0,

@@ -528,3 +528,21 @@ def test_cluster_form_matches_one_cta_kernel():
     for i in range(16):
         assert close(res[3][0][i], res[2][0][i]) and close(res[3][1][i], res[2][1][i])
     pl.close()
+
+
+def test_zero_copy_inputs_are_bitwise_equal():
+    """gato_solve with the staged kernel reading the pinned input buffer in place (no H2D operation) returns the
+    same bits as the copy-first path, cold and with every warm-start mode."""
+    from gato_python_b200.solver import WARM_RESIDENT
+    prob = CASES["iiwa50_s0"]()
+    pl = plan_of(prob)
+    out = {}
+    for zc in (1, 0):
+        pl.set_zero_copy(zc)
+        a = gpu(pl, prob)
+        b = gpu(pl, prob, warm=WARM_TRUE, lambda_in=(0.5 * a[0]).astype(np.float32))
+        c = gpu(pl, dict(prob, rho=2e-3), warm=WARM_RESIDENT)
+        out[zc] = (a, b, c)
+    for x, y in zip(out[0], out[1]):
+        assert np.array_equal(x[0], y[0]) and np.array_equal(x[1], y[1]) and x[2]["iters"] == y[2]["iters"]
+    pl.close()
