@@ -84,6 +84,7 @@ struct gato_plan {
     int smem_optin = 0;
     int staging = 1;        // v2: TMA staging of the value arrays when it fits (gato_plan_set_staging)
     int zero_copy = 1;      // gato_solve: staged kernels read the pinned input buffer in place (gato_plan_set_zero_copy)
+    int lam_zc = 0;         // where gato_solve left its last lambda: 0 = device buffer, 1 = pinned result buffer
     int lam_slot = 0;       // gato_solve ping-pongs its output between two slots of dlo ...
     bool have_lambda = false;   // ... so the previous lambda stays readable for GATO_WARM_RESIDENT
     // device: pattern maps
