@@ -283,6 +283,53 @@ class Plan:
                                                dlam_in or None, ldl, dlam_out, ddz_out, diters_out, exit_tol,
                                                int(max_iters), int(warm_start), rho, stream or None))
 
+    # -- batch, any objects exposing __cuda_array_interface__ (torch, CuPy, Numba ...), zero copies --------
+    def solve_batched_cuda(self, G_val, C_val, g, c, lam_out, dz_out, iters_out, lambda_in=None, exit_tol=1e-6,
+                           max_iters=500, warm_start=WARM_OFF, rho=0.0, stream=0):
+        """Device arrays in, device arrays out, asynchronous on `stream` (a raw cudaStream_t value).  `g` is
+        [nsys, n_z]; G_val / C_val / c / lambda_in are [nsys, n] or [n] (shared by all systems); outputs are
+        caller-allocated float32 [nsys, n_l], float32 [nsys, n_z], int32 [nsys].  Nothing is copied or
+        synchronised: this is `gato_solve_batched_device` for callers that hold framework tensors."""
+        def ptr(a, dtype, name):
+            cai = getattr(a, "__cuda_array_interface__", None)
+            if cai is None:
+                raise TypeError(f"{name} does not expose __cuda_array_interface__")
+            if np.dtype(cai["typestr"]) != np.dtype(dtype):
+                raise ValueError(f"{name} must be {np.dtype(dtype).name}, got {np.dtype(cai['typestr']).name}")
+            if cai.get("strides") is not None:
+                want, acc = [], np.dtype(dtype).itemsize
+                for n in reversed(cai["shape"]):
+                    want.insert(0, acc); acc *= n
+                if tuple(cai["strides"]) != tuple(want):
+                    raise ValueError(f"{name} must be C-contiguous")
+            return int(cai["data"][0]), tuple(cai["shape"])
+
+        pg, sg = ptr(g, np.float32, "g")
+        if len(sg) != 2 or sg[1] != self.n_z:
+            raise ValueError(f"g must be [nsys, {self.n_z}]")
+        nsys = sg[0]
+
+        def rows(a, n, name):
+            pa, sa = ptr(a, np.float32, name)
+            if sa == (n,) or sa == (1, n):
+                return pa, (0 if nsys > 1 else n)
+            if sa != (nsys, n):
+                raise ValueError(f"{name} must be [{nsys}, {n}] or [{n}], got {sa}")
+            return pa, n
+
+        pG, ldG = rows(G_val, self.nnzG, "G_val")
+        pC, ldC = rows(C_val, self.nnzC, "C_val")
+        pc, ldc = rows(c, self.n_l, "c")
+        pl_, ldl = rows(lambda_in, self.n_l, "lambda_in") if lambda_in is not None else (0, 0)
+        po, so = ptr(lam_out, np.float32, "lam_out")
+        pz, sz = ptr(dz_out, np.float32, "dz_out")
+        pi, si = ptr(iters_out, np.int32, "iters_out")
+        if so != (nsys, self.n_l) or sz != (nsys, self.n_z) or si != (nsys,):
+            raise ValueError("output arrays must be [nsys, n_l], [nsys, n_z], [nsys]")
+        self.solve_batched_device(nsys, pG, ldG, pC, ldC, pg, self.n_z, pc, ldc, po, pz, pi, dlam_in=pl_, ldl=ldl,
+                                  exit_tol=exit_tol, max_iters=max_iters, warm_start=warm_start, rho=rho,
+                                  stream=stream)
+
     # -- parity hooks ----------------------------------------------------------------------------
     def unpack(self, G_val, C_val, rho):
         G_val = _f32(G_val, (self.nnzG,)); C_val = _f32(C_val, (self.nnzC,))

@@ -546,3 +546,30 @@ def test_zero_copy_inputs_are_bitwise_equal():
     for x, y in zip(out[0], out[1]):
         assert np.array_equal(x[0], y[0]) and np.array_equal(x[1], y[1]) and x[2]["iters"] == y[2]["iters"]
     pl.close()
+
+
+def test_cuda_array_interface_entry():
+    """Plan.solve_batched_cuda: torch CUDA tensors in and out through __cuda_array_interface__, no copies,
+    asynchronous on the caller's stream; same bits as the host-buffer batched call."""
+    import torch
+    b = iiwa_like_batch(12, K=50, seed0=40)
+    pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=12)
+    ref = pl.solve_batched(b["G_val"], b["C_val"][0], b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    dev = torch.device("cuda:0")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(dev)   # noqa: E731
+    G, Cv, g, c = t(b["G_val"]), t(b["C_val"][0]), t(b["g"]), t(b["c"])
+    lam = torch.empty((12, pl.n_l), device=dev); dz = torch.empty((12, pl.n_z), device=dev)
+    it = torch.empty(12, dtype=torch.int32, device=dev)
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        pl.solve_batched_cuda(G, Cv, g, c, lam, dz, it, exit_tol=b["exit_tol"], max_iters=b["max_iters"],
+                              rho=b["rho"], stream=st.cuda_stream)
+    st.synchronize()
+    assert np.array_equal(lam.cpu().numpy(), ref[0]) and np.array_equal(dz.cpu().numpy(), ref[1])
+    assert np.array_equal(it.cpu().numpy(), ref[2])
+    with pytest.raises(ValueError):
+        pl.solve_batched_cuda(G, Cv, g, c, lam[:, :-1], dz, it)
+    with pytest.raises(ValueError):
+        pl.solve_batched_cuda(G.double(), Cv, g, c, lam, dz, it)
+    pl.close()
