@@ -252,7 +252,7 @@ int v2cl_cfg(const gato_plan* pl, ClusterCfg* out) {
     if (ncta > 16) return fail(GATO_EUNSUPPORTED, "K=%d needs %d CTAs: more than one 16-CTA cluster", pl->K, ncta);
     const int kpc = (pl->K + ncta - 1) / ncta;
     ncta = (pl->K + kpc - 1) / kpc;                      // no empty CTA at the end
-    const size_t smem = (size_t)(L::smem_floats_cl(kpc, nt) + 8) * 4;
+    const size_t smem = (size_t)(L::smem_floats_cl(kpc, nt) + 12) * 4;   // + control tail (3 mbarriers, loop state, parities)
     if (smem > (size_t)pl->smem_optin)
         return fail(GATO_EUNSUPPORTED, "cluster variant: %zu B shared memory per CTA > %d", smem, pl->smem_optin);
     out->ncta = ncta; out->kpc = kpc; out->nt = nt; out->smem = smem;

@@ -174,7 +174,8 @@ struct SolveParams2 {
     int g_diag;           // pattern of G is purely diagonal: Q_k^-1, R_k^-1 are reciprocals
     int stage_off;        // > 0: float offset of the TMA staging area in shared memory (values of C, G and g
                           // arrive by cp.async.bulk, the NEXT system's while this one iterates); 0: direct loads
-    int tail_off;         // float offset of the 32-byte control tail: mbarrier | current system | mbarrier parity
+    int tail_off;         // float offset of the 48-byte control tail: mbarrier (staging; cluster variant: reduction A)
+                          // | current system | staging parity | mbarriers B, C of the cluster variant | their parities
     int kpc;              // cluster variant: knots owned per CTA (local slots 1..kpc; 0 and kpc+1 are halos)
 };
 
@@ -199,6 +200,31 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// ---- cluster variant: remote stores that signal the RECEIVER's mbarrier (st.async, complete_tx) ---------
+// A waiter that sees the phase complete (acquire at cluster scope) sees the data: no cluster-wide barrier.
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, int cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+    return r;
+}
+__device__ __forceinline__ void st_async_f32(uint32_t raddr, float v, uint32_t rmbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f32 [%0], %1, [%2];" ::"r"(raddr),
+                 "f"(v), "r"(rmbar) : "memory");
+}
+__device__ __forceinline__ void st_async_v4(uint32_t raddr, float a, float b, float c, float d, uint32_t rmbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(
+                     raddr), "f"(a), "f"(b), "f"(c), "f"(d), "r"(rmbar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "WAITC_%=:\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONEC_%=;\n\t"
+        "bra WAITC_%=;\n\t"
+        "DONEC_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
 // A bulk copy needs 16-byte aligned addresses and sizes; rows of a [nsys][n] float array are only
 // 4-byte aligned, so the copy covers the enclosing 16-byte words (at most 12 bytes either side, inside
 // words that hold row data) and the consumer skips `lead` floats.
@@ -264,7 +290,20 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         crank = (int)cluster.block_rank();
         ncta = (int)cluster.dim_blocks().x;
     }
+    // cluster variant: the three per-iteration synchronisation points are transaction barriers of the RECEIVING
+    // CTA (A: dot partials of p.Sp, B: theta^-1 r slices of the boundary knots, C: partials of r.r~ and r~ slices)
+    uint64_t* mbA = mbar;
+    uint64_t* mbB = reinterpret_cast<uint64_t*>(smem + q.tail_off + 4);
+    uint64_t* mbC = reinterpret_cast<uint64_t*>(smem + q.tail_off + 6);
+    volatile int* parity_word = reinterpret_cast<volatile int*>(smem + q.tail_off + 8);
     if (threadIdx.x == 0) {
+        if constexpr (CL) {
+            mbar_init(mbA, 1);
+            mbar_init(mbB, 1);
+            mbar_init(mbC, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            parity_word[0] = 0;
+        }
         ctl[0] = CL ? blockIdx.x / ncta : blockIdx.x;
         ctl[1] = 0;
         if (staged) {
@@ -371,6 +410,36 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 }
             }
         };
+        // the same two pushes as remote stores that complete on the receiver's transaction barrier `mb`
+        constexpr uint32_t SIDE_BYTES = VEC ? LPK * 16u : S * 4u;     // one boundary knot's slice of an iterate
+        const uint32_t nbr_bytes = CL ? ((crank > 0 ? SIDE_BYTES : 0u) + (crank + 1 < ncta ? SIDE_BYTES : 0u)) : 0u;
+        auto push_slice_async = [&](float* left_dst, float* right_dst, const float (&v)[OWN], uint64_t* mb) {
+            // left_dst / right_dst: where the slice lands in my LEFT / RIGHT neighbour's shared memory (same offsets
+            // in every CTA), e.g. its halo slot kpc+1 / 0 of xt
+            if constexpr (CL) {
+#pragma unroll
+                for (int side = 0; side < 2; ++side) {
+                    if (!(side ? pushR : pushL)) continue;
+                    const int cta = crank + (side ? 1 : -1);
+                    const uint32_t ra = mapa_u32(smem_u32((side ? right_dst : left_dst) + po0), cta);
+                    const uint32_t rm = mapa_u32(smem_u32(mb), cta);
+                    if constexpr (VEC) {
+                        st_async_v4(ra, v[0], v[1], v[2], v[OWN - 1], rm);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < OWN; ++j)
+                            if (ovr[j]) st_async_f32(ra + 4u * j, v[j], rm);
+                    }
+                }
+            }
+        };
+        auto put_partial_async = [&](float* red, float part, uint64_t* mb) {
+            if constexpr (CL) {
+                if (lane < ncta)
+                    st_async_f32(mapa_u32(smem_u32(red + crank * NW + warp), lane), part, mapa_u32(smem_u32(mb), lane));
+            }
+        };
+        uint32_t par = CL ? (uint32_t)parity_word[0] : 0u;   // bit 0/1/2: phase parity of mbA / mbB / mbC
         // per-warp partial of a dot product -> the partial array of every CTA of the system
         auto put_partial = [&](float* red, float part) {
             if constexpr (CL) {
@@ -936,8 +1005,15 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             __syncwarp();
             apply_T(xr_k, t);
             store_own(xt_k, t);
-            push_halo(xt, t);
-            sync_all();
+            if constexpr (CL) {
+                push_slice_async(xt + (q.kpc + 1) * VS, xt, t, mbB);
+                __syncthreads();                                   // this CTA's own slices
+                if (tid == 0) mbar_expect_tx(mbB, nbr_bytes);      // + the neighbours' boundary slices
+                mbar_wait_cluster(mbB, (par >> 1) & 1u);
+                par ^= 2u;
+            } else {
+                __syncthreads();
+            }
             apply_O(xt, o);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) z[j] = r_[j] - o[j];
@@ -988,9 +1064,15 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
                 for (int j = 0; j < OWN; ++j) part = fmaf(pp[j], ups[j], part);
                 part = warp_sum32(part);
-                put_partial(redA, part);
+                if constexpr (CL) put_partial_async(redA, part, mbA); else put_partial(redA, part);
             }
-            sync_all();
+            if constexpr (CL) {
+                if (tid == 0) mbar_expect_tx(mbA, (uint32_t)(ncta * NW) * 4u);
+                mbar_wait_cluster(mbA, par & 1u);
+                par ^= 1u;
+            } else {
+                __syncthreads();
+            }
             const float v = block_partials_sum(redA, nred4);
             const float alpha = fast_div(eta, v);
 #pragma unroll
@@ -999,33 +1081,23 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 rr[j] = fmaf(-alpha, ups[j], rr[j]);
             }
             precond(rr, rt);
-            if constexpr (CL) {
-                // r~ of the boundary knots travels with the reduction's barrier: the neighbour CTA then forms
-                // p_new of its halo knot itself (same fmaf, same bits) and the p exchange needs no cluster barrier
-                if (pushL || pushR) {
-                    cg::cluster_group cluster = cg::this_cluster();
-#pragma unroll
-                    for (int side = 0; side < 2; ++side) {
-                        if (!(side ? pushR : pushL)) continue;
-                        float* rem = cluster.map_shared_rank(xq + (side ? 0 : VS), crank + (side ? 1 : -1));
-                        if constexpr (VEC) {
-                            *reinterpret_cast<float4*>(rem + po0) = make_float4(rt[0], rt[1], rt[2], rt[OWN - 1]);
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < OWN; ++j)
-                                if (ovr[j]) rem[po0 + j] = rt[j];
-                        }
-                    }
-                }
-            }
+            // cluster variant: r~ of the boundary knots travels with the reduction (the neighbour CTA then forms p_new
+            // of its halo knot itself -- same fmaf, same bits -- so the p exchange needs only a block barrier)
+            push_slice_async(xq + VS, xq, rt, mbC);
             {
                 float part = 0.f;
 #pragma unroll
                 for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], rt[j], part);
                 part = warp_sum32(part);
-                put_partial(redB, part);
+                if constexpr (CL) put_partial_async(redB, part, mbC); else put_partial(redB, part);
             }
-            sync_all();
+            if constexpr (CL) {
+                if (tid == 0) mbar_expect_tx(mbC, (uint32_t)(ncta * NW) * 4u + nbr_bytes);
+                mbar_wait_cluster(mbC, (par >> 2) & 1u);
+                par ^= 4u;
+            } else {
+                __syncthreads();
+            }
             const float eta_new = block_partials_sum(redB, nred4);
             eta_last = eta_new;
             if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
@@ -1120,6 +1192,9 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             }
         }
         stamp(p, 9);
+        if constexpr (CL) {
+            if (tid == 0) parity_word[0] = (int)par;
+        }
         if (tid == 0 && crank == 0) {
             p.iters_out[sys] = iters;
             if (p.eta_out != nullptr) p.eta_out[sys] = fabsf(eta_last);
