@@ -243,15 +243,29 @@ struct ClusterCfg { int ncta, kpc, nt; size_t smem; };
 template <int S, int C>
 int v2cl_cfg(const gato_plan* pl, ClusterCfg* out) {
     using L = gato::Layout2<S, C>;
-    const int nt = V2Menu<S>::nt[V2Menu<S>::n - 1];
-    const int maxk = (nt / 32) * L::KPW - 2;            // two of a CTA's knot slots are halo knots
-    if (maxk < 1) return fail(GATO_EUNSUPPORTED, "no cluster variant for S=%d", S);
-    int ncta = (pl->K + maxk - 1) / maxk;
-    if (ncta < 2) ncta = 2;
     if (pl->K < 2) return fail(GATO_EUNSUPPORTED, "the cluster variant of the one-CTA kernel needs K >= 2");
+    const int nt_max = V2Menu<S>::nt[V2Menu<S>::n - 1];
+    const int maxk = (nt_max / 32) * L::KPW - 2;        // two of a CTA's knot slots are halo knots
+    if (maxk < 1) return fail(GATO_EUNSUPPORTED, "no cluster variant for S=%d", S);
+    int ncta;
+    if (pl->kernel == 3 && pl->cl_override > 0) {
+        ncta = pl->cl_override;                         // explicit cluster size (gato_plan_set_cluster)
+    } else {
+        // default: CTAs of about one warp per SM sub-partition (4 warps; two of the knot slots are halos) -- the
+        // per-iteration compute of a CTA halves against the 7-warp shape while the exchange cost stays (measured)
+        const int pref = 4 * L::KPW - 2;
+        ncta = (pl->K + pref - 1) / pref;
+        if (ncta > 16) ncta = (pl->K + maxk - 1) / maxk;
+    }
+    if (ncta < 2) ncta = 2;
     if (ncta > 16) return fail(GATO_EUNSUPPORTED, "K=%d needs %d CTAs: more than one 16-CTA cluster", pl->K, ncta);
     const int kpc = (pl->K + ncta - 1) / ncta;
     ncta = (pl->K + kpc - 1) / kpc;                      // no empty CTA at the end
+    if (ncta < 2) return fail(GATO_EUNSUPPORTED, "K=%d does not split over %d CTAs", pl->K, ncta);
+    int nt = 0;
+    for (int i = 0; i < V2Menu<S>::n; ++i)
+        if ((V2Menu<S>::nt[i] / 32) * L::KPW >= kpc + 2) { nt = V2Menu<S>::nt[i]; break; }
+    if (nt == 0) return fail(GATO_EUNSUPPORTED, "%d knots per CTA do not fit the cluster variant (max %d)", kpc, maxk);
     const size_t smem = (size_t)(L::smem_floats_cl(kpc, nt) + 12) * 4;   // + control tail (3 mbarriers, loop state, parities)
     if (smem > (size_t)pl->smem_optin)
         return fail(GATO_EUNSUPPORTED, "cluster variant: %zu B shared memory per CTA > %d", smem, pl->smem_optin);
@@ -259,13 +273,9 @@ int v2cl_cfg(const gato_plan* pl, ClusterCfg* out) {
     return GATO_OK;
 }
 
-template <int S, int C>
-int launch_v2cl_sc(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
+template <int S, int C, int NT>
+int launch_v2cl_t(const ClusterCfg& cfg, gato::SolveParams2 q, cudaStream_t st) {
     using L = gato::Layout2<S, C>;
-    constexpr int NT = V2Menu<S>::nt[V2Menu<S>::n - 1];
-    ClusterCfg cfg;
-    int rc = v2cl_cfg<S, C>(pl, &cfg);
-    if (rc) return rc;
     auto kern = gato::gato_fused_solve_v2<S, C, NT, true>;
     q.stage_off = 0;
     q.tail_off = L::smem_floats_cl(cfg.kpc, NT);
@@ -286,6 +296,19 @@ int launch_v2cl_sc(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     lc.numAttrs = 1;
     GATO_CUDA(cudaLaunchKernelEx(&lc, kern, q));
     return GATO_OK;
+}
+
+template <int S, int C>
+int launch_v2cl_sc(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
+    ClusterCfg cfg;
+    int rc = v2cl_cfg<S, C>(pl, &cfg);
+    if (rc) return rc;
+    if (cfg.nt == V2Menu<S>::nt[0]) return launch_v2cl_t<S, C, V2Menu<S>::nt[0]>(cfg, q, st);
+    if (cfg.nt == V2Menu<S>::nt[1]) return launch_v2cl_t<S, C, V2Menu<S>::nt[1]>(cfg, q, st);
+    if constexpr (V2Menu<S>::n > 2) {
+        if (cfg.nt == V2Menu<S>::nt[2]) return launch_v2cl_t<S, C, V2Menu<S>::nt[2]>(cfg, q, st);
+    }
+    return fail(GATO_EUNSUPPORTED, "no cluster variant with %d threads", cfg.nt);
 }
 
 template <int S, int C>

@@ -76,7 +76,7 @@ int gato_plan_get_cluster(const gato_plan* plan, int* cluster_ctas, int* knots_p
  * system resident in one SM's registers, block barriers only; the batched path and the default whenever K
  * fits), 3 = the one-CTA kernel spread over a thread-block cluster (each CTA owns a run of knots plus two
  * halo knots; neighbour slices and dot-product partials pushed through DSMEM, cluster barriers; the default
- * for IIWA-sized states once K exceeds one SM, e.g. K = 256 -> 5 CTAs x 52 knots).  All replace the same
+ * for IIWA-sized states once K exceeds one SM, e.g. K = 256 -> 9 CTAs x 29 knots).  All replace the same
  * reference functions (parallelPCG, src/gato_pcg.cuh:441-470, and the three Schur/dz kernels,
  * src/gato_schur.cuh:462-494, 652-670, 869-879). */
 int gato_plan_set_kernel(gato_plan* plan, int kernel);

@@ -218,7 +218,7 @@ def test_default_kernel_selection():
     assert pl.kernel() == 2
     pl.close()
     pl = plan_of(CASES["iiwa256"]())          # IIWA horizons beyond one SM: the one-CTA kernel over a cluster
-    assert pl.kernel() == 3 and pl.cluster() == (5, 52)
+    assert pl.kernel() == 3 and pl.cluster() == (9, 29)     # CTAs of four warps: one per SM sub-partition
     pl.close()
     pl = plan_of(CASES["S4_K512_max_cluster"]())   # small states: the warp-per-knot cluster kernel
     assert pl.kernel() == 1
@@ -572,4 +572,18 @@ def test_cuda_array_interface_entry():
         pl.solve_batched_cuda(G, Cv, g, c, lam[:, :-1], dz, it)
     with pytest.raises(ValueError):
         pl.solve_batched_cuda(G.double(), Cv, g, c, lam, dz, it)
+    pl.close()
+
+
+@pytest.mark.parametrize("ncta", [2, 5, 8, 13, 16])
+def test_kernel3_cluster_sizes_agree(ncta):
+    """Kernel 3 at explicit cluster sizes (three thread-count variants, portable and non-portable cluster sizes)."""
+    prob = CASES["iiwa256"]() if ncta >= 5 else iiwa_like(K=57, seed=0)
+    pl = plan_of(prob)
+    pl.set_kernel(3)
+    pl.set_cluster(ncta)
+    assert pl.cluster()[0] == ncta
+    lam, dz, info = gpu(pl, prob)
+    lam_o, dz_o, io = oracle(prob)
+    assert close(lam, lam_o) and close(dz, dz_o) and abs(info["iters"] - io["iters"]) <= 1
     pl.close()
