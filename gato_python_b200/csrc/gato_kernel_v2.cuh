@@ -334,7 +334,9 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         const bool lhalo = CL && slot == 0 && b >= 0;           // redoes Q^-1, R^-1 of the previous CTA's last knot
         const bool rhalo = CL && slot == q.kpc + 1 && b < K;    // redoes phi of the next CTA's first knot
         const int nreg = CL ? q.kpc + 2 : K;            // knot regions in this CTA's shared memory
-        const int xb = CL ? slot - 1 : slot;            // iterate slot of the LEFT neighbour (own = xb + 1)
+        // iterate slot of the LEFT neighbour (own = xb + 1); lanes without a block row read slots 0..2 (their
+        // matrices are zero, the products must only stay finite)
+        const int xb = CL ? (active ? slot - 1 : 0) : slot;
         const int h = lik % H, g = lik / H;             // column group, row group (matrix mapping)
 
         // ---- shared memory carve-up ----------------------------------------------------------------
