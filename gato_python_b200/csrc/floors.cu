@@ -88,6 +88,35 @@ __global__ void k_reduce_chain(int reps, long long* out, float* sink) {
     if (threadIdx.x == 0) { out[0] = t1 - t0; sink[0] = eta; }
 }
 
+// FP32 FMA issue: 8 independent accumulator chains per thread, scalar FFMA vs packed FFMA2 (fma.rn.f32x2)
+template <bool PACKED>
+__global__ void k_fma(int reps, long long* out, float* sink) {
+    float a[16];
+    for (int i = 0; i < 16; ++i) a[i] = threadIdx.x * 1e-3f + i;
+    const float b = 1.0001f, c = 1e-3f;
+    unsigned long long p[8], bb, cc;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(b), "f"(b));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(cc) : "f"(c), "f"(c));
+    for (int i = 0; i < 8; ++i) asm("mov.b64 %0, {%1, %2};" : "=l"(p[i]) : "f"(a[2 * i]), "f"(a[2 * i + 1]));
+    __syncthreads();
+    const long long t0 = clock64();
+    for (int r = 0; r < reps; ++r) {
+        if (PACKED) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(p[i]) : "l"(p[i]), "l"(bb), "l"(cc));
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(a[i]) : "f"(a[i]), "f"(b), "f"(c));
+        }
+    }
+    const long long t1 = clock64();
+    float s = 0.f;
+    for (int i = 0; i < 16; ++i) s += a[i];
+    for (int i = 0; i < 8; ++i) s += __uint_as_float((unsigned)p[i]) + __uint_as_float((unsigned)(p[i] >> 32));
+    if (threadIdx.x == 0) out[0] = t1 - t0;
+    sink[threadIdx.x] = s;
+}
+
 __global__ void k_grid_sync(int reps, long long* out) {
     cg::grid_group g = cg::this_grid();
     g.sync();
@@ -104,7 +133,7 @@ int main() {
     long long* d_out;
     float* d_sink;
     CK(cudaMalloc(&d_out, 64));
-    CK(cudaMalloc(&d_sink, 64));
+    CK(cudaMalloc(&d_sink, 4096));
     long long h[2];
     const int reps = 2000;
 
@@ -139,8 +168,17 @@ int main() {
     CK(cudaMemcpy(h, d_out, 16, cudaMemcpyDeviceToHost));
     const double chain_ns = ns(h[0]);
 
+    // 16 FMAs per thread per round either way (16 FFMA or 8 FFMA2), 8 warps per SM = 2 per scheduler
+    double fma_cyc[2];
+    for (int pk = 0; pk < 2; ++pk) {
+        if (pk) k_fma<true><<<1, 256>>>(reps, d_out, d_sink); else k_fma<false><<<1, 256>>>(reps, d_out, d_sink);
+        CK(cudaMemcpy(h, d_out, 16, cudaMemcpyDeviceToHost));
+        fma_cyc[pk] = (double)h[0] / reps;
+    }
+
     std::printf("{\"sm_clock_khz\": %d, \"launch_us\": %.2f, \"syncthreads_ns\": %.1f, \"syncthreads_cycles\": %.1f, "
-                "\"reduce_chain_ns\": %.1f", khz, launch_us, sync_ns, sync_cyc, chain_ns);
+                "\"reduce_chain_ns\": %.1f, \"cycles_per_16_fma_per_thread_2_warps_per_scheduler\": {\"ffma\": %.1f, \"ffma2\": %.1f}",
+                khz, launch_us, sync_ns, sync_cyc, chain_ns, fma_cyc[0], fma_cyc[1]);
 
     CK(cudaFuncSetAttribute(k_cluster_sync, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     for (int push = 0; push < 2; ++push) {
