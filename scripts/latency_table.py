@@ -63,9 +63,15 @@ def main():
             row["ours_cluster_kernel"] = ours(prob, kernel=1)
         md = refrun.ref_module_dir(prob["S"], prob["C"], prob["K"])
         if md:
-            r = refrun.run_module(md, prob, testiters=50)
+            r = refrun.run_module(md, prob, testiters=50, wall_reps=100)
             row["reference_cuda_build"] = {"iters": r["iters"], "bracket_us_avg50": round(r["avg_ms"] * 1e3, 1),
-                                           "first_us": round(r["first_ms"] * 1e3, 1)}
+                                           "first_us": round(r["first_ms"] * 1e3, 1),
+                                           "python_list_call_wall_us": round(r["python_wall_s"] * 1e6, 1)}
+        dd = refrun.dropin_module_dir(prob["S"], prob["C"], prob["K"])
+        if dd:   # the same list-in / list-out Python call through OUR gpu_library module
+            r = refrun.run_module(dd, prob, testiters=50, wall_reps=100)
+            row["ours_dropin_module"] = {"iters": r["iters"], "bracket_us_avg50": round(r["avg_ms"] * 1e3, 1),
+                                         "python_list_call_wall_us": round(r["python_wall_s"] * 1e6, 1)}
         table[name] = row
         print(name, json.dumps(row), file=sys.stderr, flush=True)
     print(json.dumps(table))
