@@ -92,6 +92,7 @@ struct gato_plan {
     int *d_gdst2 = nullptr, *d_cdst2 = nullptr;   // v2: absolute shared-memory destinations
     // device: staged inputs / outputs for the host-buffer entry points
     DevBuf dG, dC, dg, dc, dl, dlo, ddz, dit, dbg;
+    DevBuf dgrid;           // kernel 4: global scratch of the cooperative-grid variant
     PinBuf hin, hout;   // pinned staging for the single-solve path
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -311,6 +312,69 @@ int launch_v2cl_sc(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     return fail(GATO_EUNSUPPORTED, "no cluster variant with %d threads", cfg.nt);
 }
 
+// ---- v2 over a cooperative grid (kernel 4): horizons beyond one 16-CTA cluster --------------------------
+// CTAs of V2Menu::nt[1] threads (four warps at S = 14), up to 30 own knots each, all co-resident; slices and
+// partials through a global scratch buffer, grid.sync() at the synchronisation points.  One system per launch.
+template <int S, int C>
+int v2grid_cfg(const gato_plan* pl, ClusterCfg* out) {
+    using L = gato::Layout2<S, C>;
+    constexpr int NT = V2Menu<S>::nt[1];
+    if (pl->K < 2) return fail(GATO_EUNSUPPORTED, "the grid variant needs K >= 2");
+    const int maxk = (NT / 32) * L::KPW - 2;
+    if (maxk < 1) return fail(GATO_EUNSUPPORTED, "no grid variant for S=%d", S);
+    int ncta = (pl->K + maxk - 1) / maxk;
+    if (ncta < 2) ncta = 2;
+    const int kpc = (pl->K + ncta - 1) / ncta;
+    ncta = (pl->K + kpc - 1) / kpc;
+    if (ncta < 2) return fail(GATO_EUNSUPPORTED, "K=%d does not split over CTAs", pl->K);
+    const size_t smem = (size_t)(L::smem_floats_cl(kpc, NT) + 12) * 4;
+    if (smem > (size_t)pl->smem_optin)
+        return fail(GATO_EUNSUPPORTED, "grid variant: %zu B shared memory per CTA > %d", smem, pl->smem_optin);
+    auto kern = gato::gato_fused_solve_v2<S, C, NT, true, true>;
+    int occ = 0;
+    GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+    const int cap = occ * (pl->sm_count > 0 ? pl->sm_count : 148);
+    if (ncta > cap || ncta > 256)
+        return fail(GATO_EUNSUPPORTED, "K=%d needs %d co-resident CTAs, the device holds %d", pl->K, ncta, cap < 256 ? cap : 256);
+    out->ncta = ncta; out->kpc = kpc; out->nt = NT; out->smem = smem;
+    return GATO_OK;
+}
+
+template <int S, int C>
+int launch_v2grid_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
+    using L = gato::Layout2<S, C>;
+    constexpr int NT = V2Menu<S>::nt[1];
+    ClusterCfg cfg;
+    int rc = v2grid_cfg<S, C>(pl, &cfg);
+    if (rc) return rc;
+    GATO_CUDA(pl->dgrid.ensure((size_t)(512 + cfg.ncta * 6 * L::VS) * sizeof(float)));
+    auto kern = gato::gato_fused_solve_v2<S, C, NT, true, true>;
+    q.stage_off = 0;
+    q.tail_off = L::smem_floats_cl(cfg.kpc, NT);
+    q.kpc = cfg.kpc;
+    q.ncta = cfg.ncta;
+    q.gbuf = (float*)pl->dgrid.p;
+    const gato::SolveParams base = q.p;
+    for (int sys = 0; sys < base.nsys; ++sys) {   // a cooperative grid holds one system: batches run back to back
+        gato::SolveParams& p = q.p;
+        p = base;
+        p.nsys = 1;
+        p.G_val = base.G_val + (long long)sys * base.ldG;
+        p.C_val = base.C_val + (long long)sys * base.ldC;
+        p.g = base.g + (long long)sys * base.ldg;
+        p.c = base.c + (long long)sys * base.ldc;
+        if (base.lambda_in) p.lambda_in = base.lambda_in + (long long)sys * base.ldl;
+        p.lambda_out = base.lambda_out + (long long)sys * base.ldlo;
+        p.dz_out = base.dz_out + (long long)sys * base.lddz;
+        p.iters_out = base.iters_out + sys;
+        if (base.eta_out) p.eta_out = base.eta_out + sys;
+        void* args[] = {(void*)&q};
+        GATO_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3((unsigned)cfg.ncta), dim3((unsigned)NT), args, cfg.smem, st));
+    }
+    return GATO_OK;
+}
+
 template <int S, int C>
 void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::vector<int>& gstart,
                   const std::vector<int>& cmap, const std::vector<int>& cstart, std::vector<int>* gdst,
@@ -395,12 +459,19 @@ int v2_nt_for(const gato_plan* pl) {
 }
 
 bool use_v2(const gato_plan* pl) {
-    if (pl->kernel == 1 || pl->kernel == 3 || (pl->kernel == 0 && pl->cl_override > 0)) return false;
+    if (pl->kernel == 1 || pl->kernel == 3 || pl->kernel == 4 || (pl->kernel == 0 && pl->cl_override > 0)) return false;
     return v2_nt_for(pl) > 0;
 }
 
 int v2cl_cfg_for(const gato_plan* pl, ClusterCfg* cfg) {
 #define X(s, c) if (pl->S == s && pl->C == c) return v2cl_cfg<s, c>(pl, cfg);
+    GATO_FOR_SIZES(X)
+#undef X
+    return fail(GATO_EUNSUPPORTED, "no kernels for S=%d C=%d", pl->S, pl->C);
+}
+
+int v2grid_cfg_for(const gato_plan* pl, ClusterCfg* cfg) {
+#define X(s, c) if (pl->S == s && pl->C == c) return v2grid_cfg<s, c>(pl, cfg);
     GATO_FOR_SIZES(X)
 #undef X
     return fail(GATO_EUNSUPPORTED, "no kernels for S=%d C=%d", pl->S, pl->C);
@@ -415,6 +486,19 @@ bool use_v2cl(const gato_plan* pl) {
     ClusterCfg cfg;
     const std::string keep = g_err;
     const bool ok = v2cl_cfg_for(pl, &cfg) == GATO_OK;
+    g_err = keep;
+    return ok;
+}
+
+// kernel 4 (the same over a cooperative grid): explicit choice, or automatic when nothing else holds the horizon
+bool use_v2grid(const gato_plan* pl) {
+    if (pl->kernel == 4) return true;
+    if (pl->kernel != 0 || pl->cl_override > 0 || use_v2(pl) || use_v2cl(pl)) return false;
+    const std::string keep = g_err;
+    LaunchCfg c1;
+    ClusterCfg cg_;
+    const bool v1_ok = cfg_for(pl, &c1) == GATO_OK;
+    const bool ok = !v1_ok && v2grid_cfg_for(pl, &cg_) == GATO_OK;
     g_err = keep;
     return ok;
 }
@@ -467,10 +551,22 @@ void v2_maps_for(const gato_plan* pl, const std::vector<int>& gmap, const std::v
 #undef X
 }
 
+int launch_solve_v2grid(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+    gato::SolveParams2 q;
+    q.p = p;
+    q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
+#define X(s, c) if (pl->S == s && pl->C == c) return launch_v2grid_sc<s, c>(pl, q, st);
+    GATO_FOR_SIZES(X)
+#undef X
+    return fail(GATO_EUNSUPPORTED, "no v2 kernels for S=%d C=%d", pl->S, pl->C);
+}
+
 // the kernel the plan selects; dumps of the Schur intermediates exist only in the cluster kernel
-int launch_auto(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+int launch_auto(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
     if (p.dbg_S == nullptr && use_v2(pl)) return launch_solve_v2(pl, p, st);
     if (p.dbg_S == nullptr && use_v2cl(pl)) return launch_solve_v2cl(pl, p, st);
+    if (p.dbg_S == nullptr && use_v2grid(pl)) return launch_solve_v2grid(pl, p, st);
     return launch_solve(pl, p, st);
 }
 

@@ -177,6 +177,8 @@ struct SolveParams2 {
     int tail_off;         // float offset of the 48-byte control tail: mbarrier (staging; cluster variant: reduction A)
                           // | current system | staging parity | mbarriers B, C of the cluster variant | their parities
     int kpc;              // cluster variant: knots owned per CTA (local slots 1..kpc; 0 and kpc+1 are halos)
+    int ncta;             // grid variant: CTAs per system
+    float* gbuf;          // grid variant: global scratch, [2][256] per-CTA dot partials | [ncta][3][2][VS] boundary slices
 };
 
 // ---- TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier) ---------------------
@@ -253,8 +255,14 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // to every CTA, and the four block barriers per iteration become cluster barriers
 // (barrier.cluster arrive.release / wait.acquire); all CTAs sum the same partials in the same order, so
 // they agree bit for bit on alpha, beta and the exit test.
-template <int S, int C, int NT, bool CL = false>
+//
+// GRID = true (implies CL): the cluster variant's decomposition over a COOPERATIVE GRID, for horizons beyond one
+// 16-CTA cluster (the job of the reference's grid-stride parallelPCG_fixed, src/gato_pcg.cuh:17-268).  The CTAs are
+// not cluster mates, so boundary slices and per-CTA dot partials travel through a small global scratch buffer and
+// the synchronisation points are grid.sync(); every CTA reduces the same partials in the same order.
+template <int S, int C, int NT, bool CL = false, bool GRID = false>
 __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 q) {
+    static_assert(!GRID || CL, "the grid variant uses the cluster variant's decomposition");
     using L = Layout2<S, C>;
     using MS = MapState<S, C>;
     using MC = MapControl<S, C>;
@@ -285,7 +293,10 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         if (v_.bytes) bulk_g2s(stg_, v_.src, v_.bytes, mbar);
     };
     int crank = 0, ncta = 1;
-    if constexpr (CL) {
+    if constexpr (GRID) {
+        ncta = q.ncta;
+        crank = (int)blockIdx.x % ncta;
+    } else if constexpr (CL) {
         cg::cluster_group cluster = cg::this_cluster();
         crank = (int)cluster.block_rank();
         ncta = (int)cluster.dim_blocks().x;
@@ -297,7 +308,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     uint64_t* mbC = reinterpret_cast<uint64_t*>(smem + q.tail_off + 6);
     volatile int* parity_word = reinterpret_cast<volatile int*>(smem + q.tail_off + 8);
     if (threadIdx.x == 0) {
-        if constexpr (CL) {
+        if constexpr (CL && !GRID) {
             mbar_init(mbA, 1);
             mbar_init(mbB, 1);
             mbar_init(mbC, 1);
@@ -387,14 +398,32 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         auto store_own = [&](float* base, const float (&v)[OWN]) { store_own_if(active, base, v); };
         // every thread of the system passes here: block barrier, or cluster barrier over all its CTAs
         auto sync_all = [&]() {
-            if constexpr (CL) cg::this_cluster().sync(); else __syncthreads();
+            if constexpr (GRID) cg::this_grid().sync();
+            else if constexpr (CL) cg::this_cluster().sync();
+            else __syncthreads();
         };
+        // grid variant: boundary slices in global memory, [cta][kind: 0 p, 1 theta^-1 r, 2 r~][side at the receiver][VS]
+        auto gslice = [&](int cta, int kind, int side) { return q.gbuf + 512 + ((cta * 3 + kind) * 2 + side) * VS; };
         // cluster variant: the boundary knots also write their slice of an iterate into the neighbour CTA's
         // halo slot (my left neighbour's slot kpc+1 / my right neighbour's slot 0) through DSMEM
         const bool pushL = CL && active && slot == 1 && crank > 0;
         const bool pushR = CL && active && slot == q.kpc && b + 1 < K;
         auto push_halo = [&](float* arr, const float (&v)[OWN]) {   // arr = xp or xt (slot 0 of the halo layout)
-            if constexpr (CL) {
+            if constexpr (GRID) {
+                const int kind = arr == xp ? 0 : (arr == xt ? 1 : 2);
+#pragma unroll
+                for (int side = 0; side < 2; ++side) {   // my slice lands in my left neighbour's RIGHT halo and vice versa
+                    if (!(side ? pushR : pushL)) continue;
+                    float* dst = gslice(crank + (side ? 1 : -1), kind, side ? 0 : 1) + po0;
+                    if constexpr (VEC) {
+                        __stcg(reinterpret_cast<float4*>(dst), make_float4(v[0], v[1], v[2], v[OWN - 1]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < OWN; ++j)
+                            if (ovr[j]) __stcg(dst + j, v[j]);
+                    }
+                }
+            } else if constexpr (CL) {
                 if (pushL || pushR) {
                     cg::cluster_group cluster = cg::this_cluster();
 #pragma unroll
@@ -412,13 +441,58 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 }
             }
         };
+        // grid variant, after the grid barrier: the boundary knots copy their neighbours' slices into the halo slots
+        // (left halo = slot 0, right halo = slot after the last own knot; xq: [0] left, [1] right)
+        auto pull_halo = [&](float* arr) {
+            if constexpr (GRID) {
+                const int kind = arr == xp ? 0 : (arr == xt ? 1 : 2);
+#pragma unroll
+                for (int side = 0; side < 2; ++side) {
+                    if (!(side ? pushR : pushL)) continue;
+                    const float* src = gslice(crank, kind, side) + po0;
+                    float* dst = (kind == 2 ? arr + side * VS : arr + (side ? slot + 1 : 0) * VS) + po0;
+                    if constexpr (VEC) {
+                        *reinterpret_cast<float4*>(dst) = __ldcg(reinterpret_cast<const float4*>(src));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < OWN; ++j)
+                            if (ovr[j]) dst[j] = __ldcg(src + j);
+                    }
+                }
+                __syncwarp();
+            }
+        };
+        // grid variant: a dot product over the whole system.  Warp partials -> one partial per CTA in global memory
+        // -> grid barrier -> every CTA adds the ncta partials in the same fixed order (same bits everywhere).
+        auto grid_dot = [&](float warp_part, int which) -> float {
+            float total = 0.f;
+            if constexpr (GRID) {
+                if (lane == 0) redA[warp] = warp_part;
+                __syncthreads();
+                if (tid == 0) {
+                    float sc = 0.f;
+                    for (int w = 0; w < NW; ++w) sc += redA[w];
+                    __stcg(q.gbuf + which * 256 + crank, sc);
+                }
+                cg::this_grid().sync();
+                if (warp == 0) {
+                    float sl = 0.f;
+                    for (int i = lane; i < ncta; i += 32) sl += __ldcg(q.gbuf + which * 256 + i);
+                    sl = warp_sum32(sl);
+                    if (lane == 0) redA[NRED - 1] = sl;
+                }
+                __syncthreads();
+                total = redA[NRED - 1];
+            }
+            return total;
+        };
         // the same two pushes as remote stores that complete on the receiver's transaction barrier `mb`
         constexpr uint32_t SIDE_BYTES = VEC ? LPK * 16u : S * 4u;     // one boundary knot's slice of an iterate
         const uint32_t nbr_bytes = CL ? ((crank > 0 ? SIDE_BYTES : 0u) + (crank + 1 < ncta ? SIDE_BYTES : 0u)) : 0u;
         auto push_slice_async = [&](float* left_dst, float* right_dst, const float (&v)[OWN], uint64_t* mb) {
             // left_dst / right_dst: where the slice lands in my LEFT / RIGHT neighbour's shared memory (same offsets
             // in every CTA), e.g. its halo slot kpc+1 / 0 of xt
-            if constexpr (CL) {
+            if constexpr (CL && !GRID) {
 #pragma unroll
                 for (int side = 0; side < 2; ++side) {
                     if (!(side ? pushR : pushL)) continue;
@@ -436,15 +510,17 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             }
         };
         auto put_partial_async = [&](float* red, float part, uint64_t* mb) {
-            if constexpr (CL) {
+            if constexpr (CL && !GRID) {
                 if (lane < ncta)
                     st_async_f32(mapa_u32(smem_u32(red + crank * NW + warp), lane), part, mapa_u32(smem_u32(mb), lane));
             }
         };
-        uint32_t par = CL ? (uint32_t)parity_word[0] : 0u;   // bit 0/1/2: phase parity of mbA / mbB / mbC
+        uint32_t par = (CL && !GRID) ? (uint32_t)parity_word[0] : 0u;   // bit 0/1/2: phase parity of mbA / mbB / mbC
         // per-warp partial of a dot product -> the partial array of every CTA of the system
         auto put_partial = [&](float* red, float part) {
-            if constexpr (CL) {
+            if constexpr (GRID) {
+                // (grid variant reduces through grid_dot)
+            } else if constexpr (CL) {
                 if (lane < ncta) cg::this_cluster().map_shared_rank(red, lane)[crank * NW + warp] = part;
             } else {
                 if (lane == 0) red[warp] = part;
@@ -1007,7 +1083,11 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             __syncwarp();
             apply_T(xr_k, t);
             store_own(xt_k, t);
-            if constexpr (CL) {
+            if constexpr (GRID) {
+                push_halo(xt, t);
+                sync_all();
+                pull_halo(xt);
+            } else if constexpr (CL) {
                 push_slice_async(xt + (q.kpc + 1) * VS, xt, t, mbB);
                 __syncthreads();                                   // this CTA's own slices
                 if (tid == 0) mbar_expect_tx(mbB, nbr_bytes);      // + the neighbours' boundary slices
@@ -1037,25 +1117,34 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             store_own(xp_k, lam);
             push_halo(xp, lam);
             sync_all();
+            pull_halo(xp);
             apply_S(xp, ups);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) rr[j] = ov[j] ? gam[j] - ups[j] : 0.f;
             sync_all();
         }
         precond(rr, rt);
+        float wpart = 0.f;   // this warp's partial of the dot product in flight (the grid variant reduces it later)
         {
             float part = 0.f;
 #pragma unroll
             for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], rt[j], part);
             part = warp_sum32(part);
             put_partial(redB, part);
+            wpart = part;
         }
 #pragma unroll
         for (int j = 0; j < OWN; ++j) pp[j] = rt[j];
         store_own(xp_k, pp);
         push_halo(xp, pp);
-        sync_all();
-        float eta = block_partials_sum(redB, nred4);
+        float eta;
+        if constexpr (GRID) {
+            eta = grid_dot(wpart, 1);            // its grid barrier also publishes the p slices
+            pull_halo(xp);
+        } else {
+            sync_all();
+            eta = block_partials_sum(redB, nred4);
+        }
         int iters = p.max_iters;
         float eta_last = eta;
         stamp(p, 7);
@@ -1066,16 +1155,22 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
                 for (int j = 0; j < OWN; ++j) part = fmaf(pp[j], ups[j], part);
                 part = warp_sum32(part);
-                if constexpr (CL) put_partial_async(redA, part, mbA); else put_partial(redA, part);
+                if constexpr (CL && !GRID) put_partial_async(redA, part, mbA);
+                if constexpr (!CL) put_partial(redA, part);
+                wpart = part;
             }
-            if constexpr (CL) {
+            float v;
+            if constexpr (GRID) {
+                v = grid_dot(wpart, 0);
+            } else if constexpr (CL) {
                 if (tid == 0) mbar_expect_tx(mbA, (uint32_t)(ncta * NW) * 4u);
                 mbar_wait_cluster(mbA, par & 1u);
                 par ^= 1u;
+                v = block_partials_sum(redA, nred4);
             } else {
                 __syncthreads();
+                v = block_partials_sum(redA, nred4);
             }
-            const float v = block_partials_sum(redA, nred4);
             const float alpha = fast_div(eta, v);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) {
@@ -1086,21 +1181,29 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             // cluster variant: r~ of the boundary knots travels with the reduction (the neighbour CTA then forms p_new
             // of its halo knot itself -- same fmaf, same bits -- so the p exchange needs only a block barrier)
             push_slice_async(xq + VS, xq, rt, mbC);
+            if constexpr (GRID) push_halo(xq, rt);
             {
                 float part = 0.f;
 #pragma unroll
                 for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], rt[j], part);
                 part = warp_sum32(part);
-                if constexpr (CL) put_partial_async(redB, part, mbC); else put_partial(redB, part);
+                if constexpr (CL && !GRID) put_partial_async(redB, part, mbC);
+                if constexpr (!CL) put_partial(redB, part);
+                wpart = part;
             }
-            if constexpr (CL) {
+            float eta_new;
+            if constexpr (GRID) {
+                eta_new = grid_dot(wpart, 1);
+                pull_halo(xq);
+            } else if constexpr (CL) {
                 if (tid == 0) mbar_expect_tx(mbC, (uint32_t)(ncta * NW) * 4u + nbr_bytes);
                 mbar_wait_cluster(mbC, (par >> 2) & 1u);
                 par ^= 4u;
+                eta_new = block_partials_sum(redB, nred4);
             } else {
                 __syncthreads();
+                eta_new = block_partials_sum(redB, nred4);
             }
-            const float eta_new = block_partials_sum(redB, nred4);
             eta_last = eta_new;
             if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
             const float beta = fast_div(eta_new, eta);
@@ -1135,6 +1238,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 if (ov[j]) p.lambda_out[(long long)sys * p.ldlo + b * S + orow[j]] = lam[j];
         }
         sync_all();
+        pull_halo(xp);
         if (active) {
             float ln[S];                                    // lambda_{b+1}; zero past the horizon
             load_row(xp + (xb + 2) * VS, ln);
@@ -1194,7 +1298,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             }
         }
         stamp(p, 9);
-        if constexpr (CL) {
+        if constexpr (CL && !GRID) {
             if (tid == 0) parity_word[0] = (int)par;
         }
         if (tid == 0 && crank == 0) {

@@ -156,7 +156,7 @@ class Plan:
         _check(lib().gato_plan_set_cluster(self._h, int(cluster_ctas)))
 
     def set_kernel(self, kernel):
-        """0 = automatic, 1 = warp-per-knot cluster kernel, 2 = one-CTA-per-system kernel, 3 = one-CTA kernel over a cluster."""
+        """0 = automatic, 1 = warp-per-knot cluster kernel, 2 = one-CTA-per-system kernel, 3 = one-CTA kernel over a cluster, 4 = over a cooperative grid."""
         _check(lib().gato_plan_set_kernel(self._h, int(kernel)))
 
     def kernel(self):

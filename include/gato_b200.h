@@ -76,7 +76,10 @@ int gato_plan_get_cluster(const gato_plan* plan, int* cluster_ctas, int* knots_p
  * system resident in one SM's registers, block barriers only; the batched path and the default whenever K
  * fits), 3 = the one-CTA kernel spread over a thread-block cluster (each CTA owns a run of knots plus two
  * halo knots; neighbour slices and dot-product partials pushed through DSMEM, cluster barriers; the default
- * for IIWA-sized states once K exceeds one SM, e.g. K = 256 -> 9 CTAs x 29 knots).  All replace the same
+ * for IIWA-sized states once K exceeds one SM, e.g. K = 256 -> 9 CTAs x 29 knots), 4 = the same decomposition
+ * over a cooperative grid (slices and partials through a global scratch buffer, grid.sync; the default when no
+ * cluster holds the horizon, e.g. K = 1000 -> 34 CTAs x 30 knots, up to one CTA per SM; this is the job of the
+ * reference's grid-stride parallelPCG_fixed, src/gato_pcg.cuh:17-268, 529-553).  All replace the same
  * reference functions (parallelPCG, src/gato_pcg.cuh:441-470, and the three Schur/dz kernels,
  * src/gato_schur.cuh:462-494, 652-670, 869-879). */
 int gato_plan_set_kernel(gato_plan* plan, int kernel);

@@ -82,7 +82,7 @@ def test_unpack_bit_exact(name):
     pl.close()
 
 
-@pytest.mark.parametrize("kernel", [1, 2, 3], ids=["cluster", "onecta", "onecta_cluster"])
+@pytest.mark.parametrize("kernel", [1, 2, 3, 4], ids=["cluster", "onecta", "onecta_cluster", "onecta_grid"])
 @pytest.mark.parametrize("name", list(CASES))
 def test_solve_vs_oracle(name, kernel):
     prob = CASES[name]()
@@ -91,7 +91,7 @@ def test_solve_vs_oracle(name, kernel):
         pl.set_kernel(kernel)
     except solver.GatoError:
         # beyond one CTA: cluster kernels only; the cluster form of the one-CTA kernel needs two knots
-        assert (kernel == 2 and name in ("iiwa256", "S4_K512_max_cluster")) or (kernel == 3 and name == "ragged_K1")
+        assert (kernel == 2 and name in ("iiwa256", "S4_K512_max_cluster")) or (kernel in (3, 4) and name == "ragged_K1")
         pytest.skip("K does not fit this kernel")
     assert pl.kernel() == kernel
     warm = WARM_REFERENCE if "warmflag" in name else 0
@@ -585,5 +585,32 @@ def test_kernel3_cluster_sizes_agree(ncta):
     assert pl.cluster()[0] == ncta
     lam, dz, info = gpu(pl, prob)
     lam_o, dz_o, io = oracle(prob)
+    assert close(lam, lam_o) and close(dz, dz_o) and abs(info["iters"] - io["iters"]) <= 1
+    pl.close()
+
+
+def test_long_horizon_cooperative_grid():
+    """Horizons beyond one 16-CTA cluster (the job of the reference's grid-stride parallelPCG_fixed,
+    src/gato_pcg.cuh:17-268): kernel 4 is selected automatically; single solve, true warm start and a small batch."""
+    prob = iiwa_like(K=1000, seed=0)
+    pl = plan_of(prob)
+    assert pl.kernel() == 4 and pl.cluster() == (34, 30)
+    lam, dz, info = gpu(pl, prob)
+    lam_o, dz_o, io = oracle(prob)
+    assert close(lam, lam_o) and close(dz, dz_o) and abs(info["iters"] - io["iters"]) <= 1
+    lam2, _, info2 = gpu(pl, dict(prob, exit_tol=1e-4), warm=WARM_TRUE, lambda_in=lam)
+    assert info2["iters"] <= 2 and close(lam2, lam)
+    g2 = np.stack([prob["g"], 0.5 * prob["g"], -prob["g"]]).astype(np.float32)
+    lb, dzb, itb, _ = pl.solve_batched(prob["G_val"], prob["C_val"], g2, prob["c"], None, prob["exit_tol"],
+                                       prob["max_iters"], 0, prob["rho"])
+    assert np.array_equal(lb[0], lam) and np.array_equal(dzb[0], dz) and itb[0] == info["iters"]
+    lam_o2, dz_o2, io2 = oracle(dict(prob, g=g2[2]))
+    assert close(lb[2], lam_o2) and close(dzb[2], dz_o2) and abs(int(itb[2]) - io2["iters"]) <= 1
+    pl.close()
+    small = iiwa_like(S=4, C=2, K=2000, seed=1, preset="mild")      # small states, beyond kernel 1's 512 knots
+    pl = plan_of(small)
+    assert pl.kernel() == 4
+    lam, dz, info = gpu(pl, small)
+    lam_o, dz_o, io = oracle(small)
     assert close(lam, lam_o) and close(dz, dz_o) and abs(info["iters"] - io["iters"]) <= 1
     pl.close()
