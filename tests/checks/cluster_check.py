@@ -1,8 +1,8 @@
 """Kernel 3 (the one-CTA kernel over a thread-block cluster) vs the oracle and vs kernel 1; timing."""
 import os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "scripts"))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests", "checks"))
 import torch
 from gato_python_b200 import Plan
 from gato_python_b200.problems import iiwa_like, pendulum5

@@ -1,7 +1,7 @@
 """First-light check on a B200: CUDA path vs the NumPy oracle (and the reference build if present)."""
 import os, sys, time
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 from gato_python_b200 import Plan
 from gato_python_b200.problems import pendulum5, iiwa_like

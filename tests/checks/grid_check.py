@@ -1,8 +1,8 @@
 """Kernel 4 (the register-resident kernel over a cooperative grid) vs the oracle; timing."""
 import os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "scripts"))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests", "checks"))
 import torch
 from gato_python_b200 import Plan
 from gato_python_b200.problems import iiwa_like

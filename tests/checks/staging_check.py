@@ -1,8 +1,8 @@
 """TMA-staged persistent v2 vs direct loads: bitwise equality and timing (single solve + batch)."""
 import os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "scripts"))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests", "checks"))
 import torch
 from gato_python_b200 import Plan
 from gato_python_b200.problems import iiwa_like, iiwa_like_batch_fast

@@ -1,7 +1,7 @@
 """v2 (one CTA per system) vs v1 (cluster) vs the NumPy oracle; kernel-only timing and phase stamps."""
 import os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import torch
 from gato_python_b200 import Plan
