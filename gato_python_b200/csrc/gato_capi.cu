@@ -83,7 +83,6 @@ struct gato_plan {
     int sm_count = 0;
     int smem_optin = 0;
     int staging = 1;        // v2: TMA staging of the value arrays when it fits (gato_plan_set_staging)
-    int pcg1 = 0;           // v2: single-reduction PCG (gato_plan_set_pcg)
     int zero_copy = 1;      // gato_solve: staged kernels read the pinned input buffer in place (gato_plan_set_zero_copy)
     int lam_zc = 0;         // where gato_solve left its last lambda: 0 = device buffer, 1 = pinned result buffer
     int lam_slot = 0;       // gato_solve ping-pongs its output between two slots of dlo ...
@@ -196,13 +195,10 @@ int v2_pick_nt(const gato_plan* pl) {   // smallest menu entry that holds K knot
     return 0;
 }
 
-template <int S, int C, int NT, bool PCG1 = false>
+template <int S, int C, int NT>
 int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     using L = gato::Layout2<S, C>;
-    if constexpr (!PCG1) {
-        if (pl->pcg1) return launch_v2_t<S, C, NT, true>(pl, q, st);
-    }
-    auto kern = gato::gato_fused_solve_v2<S, C, NT, false, false, PCG1>;
+    auto kern = gato::gato_fused_solve_v2<S, C, NT>;
     const int core = L::smem_floats(q.p.K, NT);
     // TMA staging of the C / G / g values (+ 16 bytes for the mbarrier) when it fits beside the system
     const int stage = gato::stage_len(q.nnzC) + gato::stage_len(q.nnzG) + gato::stage_len(pl->n_z);
@@ -526,7 +522,7 @@ bool v2_stages(const gato_plan* pl) {
 }
 
 int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
-    gato::SolveParams2 q{};
+    gato::SolveParams2 q;
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
@@ -537,7 +533,7 @@ int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_
 }
 
 int launch_solve_v2cl(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
-    gato::SolveParams2 q{};
+    gato::SolveParams2 q;
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
@@ -556,7 +552,7 @@ void v2_maps_for(const gato_plan* pl, const std::vector<int>& gmap, const std::v
 }
 
 int launch_solve_v2grid(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
-    gato::SolveParams2 q{};
+    gato::SolveParams2 q;
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;

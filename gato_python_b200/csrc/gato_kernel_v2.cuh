@@ -260,10 +260,9 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // 16-CTA cluster (the job of the reference's grid-stride parallelPCG_fixed, src/gato_pcg.cuh:17-268).  The CTAs are
 // not cluster mates, so boundary slices and per-CTA dot partials travel through a small global scratch buffer and
 // the synchronisation points are grid.sync(); every CTA reduces the same partials in the same order.
-template <int S, int C, int NT, bool CL = false, bool GRID = false, bool PCG1 = false>
+template <int S, int C, int NT, bool CL = false, bool GRID = false>
 __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 q) {
     static_assert(!GRID || CL, "the grid variant uses the cluster variant's decomposition");
-    static_assert(!PCG1 || !CL, "the single-reduction PCG exists for the one-CTA kernel only");
     using L = Layout2<S, C>;
     using MS = MapState<S, C>;
     using MC = MapControl<S, C>;
@@ -1149,65 +1148,6 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         int iters = p.max_iters;
         float eta_last = eta;
         stamp(p, 7);
-        if constexpr (PCG1) {
-            // ---- single-reduction PCG (Chronopoulos & Gear): the same Krylov iterates as the loop below in exact
-            // arithmetic, with w = S r~ formed BEFORE the reduction so that r.r~ and r~.w share one reduction:
-            //   p = r~ + beta p;  s = w + beta s;  lambda += alpha p;  r -= alpha s;  r~ = P^-1 r;  w = S r~;
-            //   eta' = r.r~, delta = r~.w  (one reduction);  exit on |eta'| < tol (same rule, same 0-based index);
-            //   beta = eta'/eta;  alpha = eta' / (delta - beta eta' / alpha)
-            // xp holds r~ here (p and s = S p live in registers only).  3 block barriers + 1 reduction chain per
-            // iteration instead of 4 + 2 (src/gato_pcg.cuh:315-437 pays 4 grid.sync + 2 atomics).
-            float ss[OWN];
-            auto two_dots = [&](float& d0, float& d1) {   // d0 = r.r~, d1 = r~.w over the whole system
-                float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-                for (int j = 0; j < OWN; ++j) { a0 = fmaf(rr[j], rt[j], a0); a1 = fmaf(rt[j], ups[j], a1); }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-                    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
-                }
-                if (lane == 0) { redA[warp] = a0; redB[warp] = a1; }
-                __syncthreads();
-                d0 = block_partials_sum(redA, nred4);
-                d1 = block_partials_sum(redB, nred4);
-            };
-            // xp holds p0 = r~0 (stored and published above): w0 = S r~0
-            apply_S(xp, ups);
-            float delta;
-            {   // eta = r0.r~0 is known; only delta goes through redA (redB may still be being read for eta)
-                float a1 = 0.f;
-#pragma unroll
-                for (int j = 0; j < OWN; ++j) a1 = fmaf(rt[j], ups[j], a1);
-                a1 = warp_sum32(a1);
-                if (lane == 0) redA[warp] = a1;
-                __syncthreads();
-                delta = block_partials_sum(redA, nred4);
-            }
-            float alpha = fast_div(eta, delta), beta = 0.f;
-#pragma unroll
-            for (int j = 0; j < OWN; ++j) { pp[j] = 0.f; ss[j] = 0.f; }
-            for (int it = 0; it < p.max_iters; ++it) {
-#pragma unroll
-                for (int j = 0; j < OWN; ++j) {
-                    pp[j] = fmaf(beta, pp[j], rt[j]);
-                    ss[j] = fmaf(beta, ss[j], ups[j]);
-                    lam[j] = fmaf(alpha, pp[j], lam[j]);
-                    rr[j] = fmaf(-alpha, ss[j], rr[j]);
-                }
-                precond(rr, rt);
-                store_own(xp_k, rt);
-                __syncthreads();
-                apply_S(xp, ups);
-                float eta_new;
-                two_dots(eta_new, delta);
-                eta_last = eta_new;
-                if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
-                beta = fast_div(eta_new, eta);
-                alpha = fast_div(eta_new, fmaf(-beta, fast_div(eta_new, alpha), delta));
-                eta = eta_new;
-            }
-        } else
         for (int it = 0; it < p.max_iters; ++it) {
             apply_S(xp, ups);
             {

@@ -20,7 +20,7 @@ WARM_OFF, WARM_REFERENCE, WARM_TRUE, WARM_RESIDENT = 0, 1, 2, 3
 SYMBOLS = [
     "gato_supported_sizes", "gato_last_error", "gato_device_count", "gato_plan_create",
     "gato_plan_create_blocks", "gato_solve_sequence",
-    "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel", "gato_plan_set_pipeline", "gato_plan_set_staging", "gato_plan_set_pcg", "gato_plan_set_zero_copy",
+    "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel", "gato_plan_set_pipeline", "gato_plan_set_staging", "gato_plan_set_zero_copy",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -59,7 +59,6 @@ def lib():
     L.gato_plan_set_kernel.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_pipeline.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_staging.argtypes = [C.c_void_p, C.c_int]
-    L.gato_plan_set_pcg.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_zero_copy.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
     L.gato_solve.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_int,
@@ -170,11 +169,6 @@ class Plan:
     def set_staging(self, on):
         """One-CTA kernel: TMA staging of the value arrays (default on when it fits); results are identical."""
         _check(lib().gato_plan_set_staging(self._h, int(bool(on))))
-
-    def set_pcg(self, variant):
-        """One-CTA kernel: 0 = the reference's PCG update order (default), 1 = single-reduction PCG
-        (one reduction and three block barriers per iteration)."""
-        _check(lib().gato_plan_set_pcg(self._h, int(variant)))
 
     def set_zero_copy(self, on):
         """solve(): staged kernels read the pinned input buffer in place over PCIe (default on); same results."""

@@ -92,13 +92,6 @@ int gato_plan_get_kernel(const gato_plan* plan);
  * (src/gato_schur.cuh:674-743). */
 int gato_plan_set_staging(gato_plan* plan, int on);
 
-/* One-CTA kernel only: PCG formulation.  0 (default) = the reference's update order (src/gato_pcg.cuh:315-437:
- * two reductions and four synchronisation points per iteration); 1 = single-reduction PCG (Chronopoulos-Gear:
- * w = S P^-1 r is formed before the reduction, so r.P^-1 r and P^-1 r.w share ONE reduction and an iteration
- * needs three block barriers).  Same Krylov iterates in exact arithmetic, same exit rule and iteration
- * numbering; FP32 rounding differs (lambda/dz within the 1e-4 bar, iteration count within +-1 in the tests). */
-int gato_plan_set_pcg(gato_plan* plan, int variant);
-
 /* gato_solve only: when the kernel stages its inputs with TMA, let those bulk copies read the plan's pinned
  * host staging buffer in place over PCIe instead of copying it to the device first (default on).  Removes
  * one of the two DMA operations of the reference's bracket (the H2D of gpu_library.cu:150-157).  Same results. */
