@@ -4,4 +4,4 @@ python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pyte
 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -n 3 gpurun_out/smoke.log
 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err; echo "bench rc=$?"
 tail -c 1500 gpurun_out/bench_ours.json
-bash scripts/gpu_sanitize.sh
+python tests/checks/all_kernels_check.py > gpurun_out/all_kernels_check.log 2>&1; echo "all kernels rc=$?"; tail -n 14 gpurun_out/all_kernels_check.log

@@ -1,9 +1,8 @@
-"""One pass over every kernel (1, 2, 2 staged/persistent, 3, 4, unpack) on small inputs, meant to run under
-compute-sanitizer (memcheck / racecheck / synccheck / initcheck); prints one line per case and checks the
-result against the oracle so that a sanitizer-clean run is also a correct one.
+"""One pass over every kernel (1, 2 direct, 2 persistent with TMA staging, 3, 4) on small inputs, each result
+checked against the oracle; one line per case.  Written to run under compute-sanitizer (memcheck / racecheck /
+synccheck), which this GPU pool keeps closed -- so it runs plain, as the all-kernels correctness pass.
 
-    compute-sanitizer --tool memcheck  python tests/checks/sanitize_run.py
-    compute-sanitizer --tool racecheck python tests/checks/sanitize_run.py
+    python tests/checks/all_kernels_check.py [k2]
 """
 import os
 import sys
