@@ -869,6 +869,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         constexpr int NLOC = (H == 2) ? VS + HALFP : 3 * VS;
         constexpr int MAIN0 = VS;                      // first local column of the main block (both layouts)
         float Sm[R][NLOC], Tm[R][HALFP];
+        // register row i of an h = 1 lane holds matrix row g*R + hrow(i) (h = 0: g*R + i)
+        auto hrow = [](int i) { return (i + OWN < R) ? i + OWN : (i >= OWN ? i - OWN : i); };
         {
             // own-row mapping (OWN rows x all columns) -> matrix mapping (R rows x own column half):
             // the two lanes of a row group swap the quadrants they do not need
@@ -886,6 +888,16 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                             const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
                             mm[j][l] = h ? recv : own[j][l];                                   // rows [0, OWN)
                             if (OWN + j < R) mm[OWN + j][l] = h ? own[j][HALFU + l] : recv;    // rows [OWN, R)
+                        }
+                    // h = 1 keeps its register rows i and OWN + i swapped (hrow), so that the row pair a lane keeps /
+                    // sends in `scatter` sits in the same registers for both column groups (no selects in the loop)
+#pragma unroll
+                    for (int i = 0; i + OWN < R; ++i)
+#pragma unroll
+                        for (int l = 0; l < HALFU; ++l) {
+                            const float lo = mm[i][l], hi = mm[OWN + i][l];
+                            mm[i][l] = h ? hi : lo;
+                            mm[OWN + i][l] = h ? lo : hi;
                         }
                 } else {
 #pragma unroll
@@ -931,7 +943,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                     for (int i = 0; i < R; ++i) {
 #pragma unroll
                         for (int ci = 0; ci < VS / 4; ++ci) {
-                            const float4 t = reinterpret_cast<const float4*>(phiR + (g * R + i) * VS)[ci];
+                            const float4 t = reinterpret_cast<const float4*>(phiR + (g * R + hrow(i)) * VS)[ci];
                             const float e[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
                             for (int u = 0; u < 4; ++u)
@@ -959,10 +971,12 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             if (H == 2) {
 #pragma unroll
                 for (int j = 0; j < OWN; ++j) {   // h = 0 keeps rows [0, OWN), h = 1 keeps rows [OWN, R)
-                    const float hi = (OWN + j < R) ? acc[OWN + j] : 0.f;
-                    const float send = h ? acc[j] : hi;
-                    const float mine = h ? hi : acc[j];
-                    out[j] = mine + __shfl_xor_sync(0xffffffffu, send, 1);
+                    if (OWN + j < R) {            // registers j / OWN + j = the row kept / sent (see hrow)
+                        out[j] = acc[j] + __shfl_xor_sync(0xffffffffu, acc[OWN + j], 1);
+                    } else {                      // a row only h = 0 keeps: h = 1 holds its other half in register j
+                        const float recv = __shfl_xor_sync(0xffffffffu, acc[j], 1);
+                        out[j] = h ? 0.f : acc[j] + recv;
+                    }
                 }
             } else {
 #pragma unroll
