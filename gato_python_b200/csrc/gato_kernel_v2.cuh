@@ -119,8 +119,9 @@ __device__ __forceinline__ float warp_sum32(float v) {
 
 // fixed-order sum of the per-warp partials (16-byte broadcast loads; same bits in every thread)
 __device__ __forceinline__ float block_partials_sum(const float* red, int nw4) {
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    for (int i = 0; i < nw4; ++i) {
+    const float4 v0 = reinterpret_cast<const float4*>(red)[0];   // nw4 >= 1
+    float s0 = v0.x, s1 = v0.y, s2 = v0.z, s3 = v0.w;
+    for (int i = 1; i < nw4; ++i) {
         const float4 v = reinterpret_cast<const float4*>(red)[i];
         s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
     }
@@ -159,12 +160,17 @@ __device__ __forceinline__ void gj_invert_knot(float (&a)[M::N][M::D], int lik, 
 
 // eta / v without the IEEE division subroutine: reciprocal seed + one residual correction (the
 // quotient is correctly rounded except in rare last-bit cases; operands are far from the range ends)
-__device__ __forceinline__ float fast_div(float a, float b) {
+__device__ __forceinline__ float rcp_seed(float b) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+    return r;
+}
+// r = rcp_seed(b), formed by the caller before a becomes known (takes the MUFU off the dependent chain)
+__device__ __forceinline__ float fast_div_seeded(float a, float b, float r) {
     const float qv = a * r;
     return fmaf(fmaf(-b, qv, a), r, qv);
 }
+__device__ __forceinline__ float fast_div(float a, float b) { return fast_div_seeded(a, b, rcp_seed(b)); }
 
 struct SolveParams2 {
     SolveParams p;        // same arguments as the cluster kernel; gmap/cmap are unused here
@@ -1191,6 +1197,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 lam[j] = fmaf(alpha, pp[j], lam[j]);
                 rr[j] = fmaf(-alpha, ups[j], rr[j]);
             }
+            const float eta_seed = rcp_seed(eta);   // for beta = eta_new / eta: eta is known before the reduction below
             precond(rr, rt);
             // cluster variant: r~ of the boundary knots travels with the reduction (the neighbour CTA then forms p_new
             // of its halo knot itself -- same fmaf, same bits -- so the p exchange needs only a block barrier)
@@ -1220,7 +1227,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             }
             eta_last = eta_new;
             if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
-            const float beta = fast_div(eta_new, eta);
+            const float beta = fast_div_seeded(eta_new, eta, eta_seed);
 #pragma unroll
             for (int j = 0; j < OWN; ++j) pp[j] = fmaf(beta, pp[j], rt[j]);
             store_own(xp_k, pp);
