@@ -43,19 +43,26 @@ def _lib_sources():
     return srcs
 
 
-def build_library(force=False, extra_sc=None, verbose=False):
-    """Compile libgato_b200.so; returns its path."""
+#: (STATE_SIZE, CONTROL_SIZE) pairs every build of the library carries (csrc/gato_capi.cu, GATO_FOR_SIZES)
+BUILTIN_SIZES = [(2, 1), (4, 2), (7, 3), (14, 7)]
+
+
+def build_library(force=False, extra_sc=None, verbose=False, out=None):
+    """Compile libgato_b200.so (or, with `out`, a second copy elsewhere -- e.g. one that carries an extra
+    (STATE_SIZE, CONTROL_SIZE) pair in every kernel family); returns its path."""
     srcs = _lib_sources()
-    if not force and not _stale(LIB, srcs):
-        return LIB
+    target = out or LIB
+    if not force and not _stale(target, srcs):
+        return target
+    os.makedirs(os.path.dirname(target), exist_ok=True)
     cmd = [_nvcc()] + ARCH + COMMON
     if extra_sc:
         cmd += [f"-DGATO_EXTRA_S={int(extra_sc[0])}", f"-DGATO_EXTRA_C={int(extra_sc[1])}"]
     if verbose:
         cmd += ["-Xptxas", "-v"]
-    cmd += [os.path.join(CSRC, "gato_capi.cu"), "-o", LIB]
+    cmd += [os.path.join(CSRC, "gato_capi.cu"), "-o", target]
     subprocess.run(cmd, check=True)
-    return LIB
+    return target
 
 
 def module_dir(S, C, K):
@@ -68,18 +75,22 @@ def build_module(S, C, K, force=False):
     install.bash:20)."""
     import pybind11
 
-    build_library()
     out_dir = module_dir(S, C, K)
     os.makedirs(out_dir, exist_ok=True)
+    if (S, C) in BUILTIN_SIZES:
+        lib, lib_dir, rpath = build_library(), HERE, "$ORIGIN/../../gato_python_b200"
+    else:   # any other STATE_SIZE / CONTROL_SIZE: the module gets its own copy of the library with that pair compiled in
+        lib = build_library(extra_sc=(S, C), out=os.path.join(out_dir, "libgato_b200.so"))
+        lib_dir, rpath = out_dir, "$ORIGIN"
     target = os.path.join(out_dir, "gpu_library" + sysconfig.get_config_var("EXT_SUFFIX"))
     src = os.path.join(CSRC, "gpu_library.cu")
-    if not force and not _stale(target, [src, LIB]):
+    if not force and not _stale(target, [src, lib]):
         return out_dir
     cmd = [_nvcc()] + ARCH + COMMON + [
         f"-DSTATE_SIZE={S}", f"-DCONTROL_SIZE={C}", f"-DKNOT_POINTS={K}",
         "-I" + sysconfig.get_paths()["include"], "-I" + pybind11.get_include(),
-        src, "-o", target, "-L" + HERE, "-lgato_b200",
-        "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../../gato_python_b200",
+        src, "-o", target, "-L" + lib_dir, "-lgato_b200",
+        "-Xlinker", "-rpath", "-Xlinker", rpath,
     ]
     subprocess.run(cmd, check=True)
     return out_dir

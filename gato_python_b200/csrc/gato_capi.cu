@@ -404,7 +404,12 @@ void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::
     }
 }
 
+// -DGATO_EXTRA_S/-DGATO_EXTRA_C add one more (STATE_SIZE, CONTROL_SIZE) pair to every kernel family
+#if GATO_EXTRA_S > 0
+#define GATO_FOR_SIZES(X) X(2, 1) X(4, 2) X(7, 3) X(14, 7) X(GATO_EXTRA_S, GATO_EXTRA_C)
+#else
 #define GATO_FOR_SIZES(X) X(2, 1) X(4, 2) X(7, 3) X(14, 7)
+#endif
 
 bool size_supported(int S, int C) {
 #define X(s, c) if (S == s && C == c) return true;
