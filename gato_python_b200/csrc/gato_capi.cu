@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -72,6 +73,13 @@ struct PinBuf {
     void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
 };
 
+// every entry point that touches the device runs on the plan's device, whatever the caller's current one is
+struct DeviceGuard {
+    int prev = 0;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+
 }  // namespace
 
 struct gato_plan {
@@ -83,6 +91,7 @@ struct gato_plan {
     int sm_count = 0;
     int smem_optin = 0;
     int staging = 1;        // v2: TMA staging of the value arrays when it fits (gato_plan_set_staging)
+    int precond = 0;        // GATO_PRECOND_STAIR / GATO_PRECOND_BLOCK_JACOBI (gato_plan_set_preconditioner)
     int zero_copy = 1;      // gato_solve: staged kernels read the pinned input buffer in place (gato_plan_set_zero_copy)
     int lam_zc = 0;         // where gato_solve left its last lambda: 0 = device buffer, 1 = pinned result buffer
     int lam_slot = 0;       // gato_solve ping-pongs its output between two slots of dlo ...
@@ -102,6 +111,9 @@ struct gato_plan {
     cudaStream_t pstream[kPipe] = {};
     cudaEvent_t pev[kPipe] = {};
     cudaEvent_t ev_shared = nullptr;
+    // one-CTA kernel: resident CTAs per SM for the shared-memory size this plan launches with (computed once per
+    // size; per plan, not per process: plans of different horizons / devices do not disturb each other)
+    mutable int occ_smem = -1, occ_val = 0;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -209,18 +221,27 @@ int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     q.kpc = q.p.K;
     const size_t smem = (size_t)(q.tail_off + tail) * 4;
     // persistent grid: as many CTAs as are resident at once, each walking systems i, i + grid, ...
-    constexpr int kMaxDev = 64;   // the attribute is per device: cache (smem -> occupancy) per device
-    static int occ_smem[kMaxDev], occ_val[kMaxDev];
-    const int di = pl->device % kMaxDev;
-    if (occ_smem[di] != (int)smem) {
+    // MaxDynamicSharedMemorySize is state of (function, device): it is raised ONCE per device to the opt-in maximum
+    // (under a lock), so host threads driving plans of different shared-memory sizes never lower it under each other.
+    {
+        constexpr int kMaxDev = 64;
+        static std::mutex mu;
+        static bool raised[kMaxDev];
+        std::lock_guard<std::mutex> lk(mu);
+        const int di = pl->device % kMaxDev;
+        if (!raised[di]) {
+            GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_optin));
+            raised[di] = true;
+        }
+    }
+    if (pl->occ_smem != (int)smem) {
         int occ = 0;
-        GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
         if (occ < 1) return fail(GATO_EUNSUPPORTED, "one-CTA kernel does not fit an SM (%zu B shared memory)", smem);
-        occ_smem[di] = (int)smem;
-        occ_val[di] = occ;
+        pl->occ_smem = (int)smem;
+        pl->occ_val = occ;
     }
-    const int resident = occ_val[di] * (pl->sm_count > 0 ? pl->sm_count : 148);
+    const int resident = pl->occ_val * (pl->sm_count > 0 ? pl->sm_count : 148);
     const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
     kern<<<grid, NT, smem, st>>>(q);
     GATO_CUDA(cudaGetLastError());

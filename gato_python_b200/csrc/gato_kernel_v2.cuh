@@ -1096,11 +1096,17 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         float* xz_k = xz + slot * VS;
         float* xt_k = xt + (xb + 1) * VS;
         float* xp_k = xp + (xb + 1) * VS;
-        // r~ = P^-1 r = theta^-1 (r - O theta^-1 r); contains one block barrier
+        // r~ = P^-1 r = theta^-1 (r - O theta^-1 r); contains one block barrier.  Block-Jacobi (p.precond = 1, the
+        // reference's SS_PRECON = 0, src/gato_schur.cuh:407-429 without :496): r~ = theta^-1 r, the knot's own
+        // lanes only -- no exchange, no barrier.
         auto precond = [&](const float (&r_)[OWN], float (&out)[OWN]) {
             float t[OWN], o[OWN], z[OWN];
             store_own(xr_k, r_);
             __syncwarp();
+            if (p.precond) {
+                apply_T(xr_k, out);
+                return;
+            }
             apply_T(xr_k, t);
             store_own(xt_k, t);
             if constexpr (GRID) {

@@ -48,6 +48,7 @@ struct SolveParams {
     float* dbg_S; float* dbg_P; float* dbg_gamma; float* dbg_Ginv;
     long long* dbg_clk;                  // [16] globaltimer ns at phase boundaries (system 0, rank 0), or null
     int K, nsys, max_iters, warm;        // warm: 0/1 = reference behaviour (lambda_in ignored), 2 = true warm start
+    int precond;                         // 0 = symmetric stair (the reference as shipped), 1 = block-Jacobi only (SS_PRECON=0)
     float rho, exit_tol;
 };
 
@@ -407,13 +408,13 @@ __global__ void __launch_bounds__(MAXW * 32, 1) gato_fused_solve(const SolvePara
             if (active && rowS) {
                 if (blk == 0) {
                     sv = kn[L::oPhi + col * S + r];
-                    pv = -kn[L::oPL + col * S + r];
+                    pv = p.precond ? 0.f : -kn[L::oPL + col * S + r];      // block-Jacobi: no off-diagonal blocks
                 } else if (blk == 1) {
                     sv = kn[L::oTh + col * S + r];
                     pv = kn[L::oThi + col * S + r];
                 } else if (blk == 2 && hasNext) {
                     sv = nxt[L::oPhi + r * S + col];        // S[b,right] = phi_{b+1}^T
-                    pv = -nxt[L::oPL + r * S + col];        // P^-1[b,right] = -PL_{b+1}^T
+                    pv = p.precond ? 0.f : -nxt[L::oPL + r * S + col];     // P^-1[b,right] = -PL_{b+1}^T
                 }
             }
             Srow[k] = sv;

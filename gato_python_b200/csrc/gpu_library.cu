@@ -15,6 +15,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -41,11 +42,35 @@ struct Cache {
     ~Cache() { /* the CUDA context may already be gone at interpreter exit: leak the plan */ }
 } g_cache;
 
+// Threading.  The reference holds the GIL for the whole call (SURVEY 8b "Threading"), which serialises its callers.
+// Here the GIL is released around the device work, so the process-global plan cache and the plan's staging buffers
+// are guarded by g_mu instead: a call takes it AFTER dropping the GIL (never the other way round) and holds it
+// across plan lookup / re-creation and the solve; errors are carried out of the locked region and raised with the
+// GIL held.
+std::mutex g_mu;
+
+struct Err {
+    int rc = GATO_OK;
+    std::string msg;
+    void set(int rc_) { if (rc_ != GATO_OK && rc == GATO_OK) { rc = rc_; msg = gato_last_error(); } }
+    void raise() const {
+        if (rc == GATO_OK) return;
+        if (rc == GATO_EINVAL || rc == GATO_EPATTERN) throw py::value_error(msg);
+        throw std::runtime_error("gato_b200: " + msg + " (code " + std::to_string(rc) + ")");
+    }
+};
+
 void check(int rc) {
-    if (rc == GATO_OK) return;
-    const std::string msg = gato_last_error();
-    if (rc == GATO_EINVAL || rc == GATO_EPATTERN) throw py::value_error(msg);
-    throw std::runtime_error("gato_b200: " + msg + " (code " + std::to_string(rc) + ")");
+    Err e;
+    e.set(rc);
+    e.raise();
+}
+
+template <class F>
+void locked_nogil(F&& f) {
+    py::gil_scoped_release nogil;
+    std::lock_guard<std::mutex> lk(g_mu);
+    f();
 }
 
 bool quiet() {
@@ -53,16 +78,18 @@ bool quiet() {
     return q && q[0] && q[0] != '0';
 }
 
+// call with g_mu held; nullptr + err on failure
 gato_plan* plan_for(const std::vector<int>& G_row, const std::vector<int>& G_col,
-                    const std::vector<int>& C_row, const std::vector<int>& C_col) {
+                    const std::vector<int>& C_row, const std::vector<int>& C_col, Err* err) {
     Cache& c = g_cache;
     if (c.plan && c.G_row == G_row && c.G_col == G_col && c.C_row == C_row && c.C_col == C_col)
         return c.plan;
     if (c.plan) { gato_plan_destroy(c.plan); c.plan = nullptr; }
     int dev = 0;
     if (const char* d = std::getenv("GATO_B200_DEVICE")) dev = std::atoi(d);
-    check(gato_plan_create(kS, kC, kK, G_row.data(), G_col.data(), (int)G_col.size(), C_row.data(),
-                           C_col.data(), (int)C_col.size(), dev, 1, &c.plan));
+    err->set(gato_plan_create(kS, kC, kK, G_row.data(), G_col.data(), (int)G_col.size(), C_row.data(),
+                              C_col.data(), (int)C_col.size(), dev, 1, &c.plan));
+    if (err->rc) { c.plan = nullptr; return nullptr; }
     c.G_row = G_row; c.G_col = G_col; c.C_row = C_row; c.C_col = C_col;
     return c.plan;
 }
@@ -91,31 +118,33 @@ py::tuple linsys_solve(std::vector<int> G_row, std::vector<int> G_col, std::vect
     check_sizes(G_row.size(), G_col.size(), G_val.size(), C_row.size(), C_col.size(), C_val.size(),
                 g_val.size(), c_val.size(), input_lambda.size());
     if (testiters < 1) throw py::value_error("testiters must be >= 1");
-    gato_plan* plan = plan_for(G_row, G_col, C_row, C_col);
     std::vector<float> lambda(input_lambda.begin(), input_lambda.begin() + kNl), lam_out(kNl), dz(kNz);
-    const int warm = !warm_start ? GATO_WARM_OFF
-                                 : (g_cache.true_warm ? GATO_WARM_TRUE : GATO_WARM_REFERENCE);
     double total = 0.0;
     int first_iters = 0;
-    float first_ms = 0.f;
-    {
-        py::gil_scoped_release nogil;
+    float first_ms = 0.f, avg_ms = 0.f;
+    Err err;
+    locked_nogil([&] {
+        gato_plan* plan = plan_for(G_row, G_col, C_row, C_col, &err);
+        if (!plan) return;
+        const int warm = !warm_start ? GATO_WARM_OFF
+                                     : (g_cache.true_warm ? GATO_WARM_TRUE : GATO_WARM_REFERENCE);
         for (int i = 0; i < testiters; ++i) {   // the reference repeats the whole solve (gpu_library.cu:169-192)
             int iters = 0;
             float ms = 0.f;
-            int rc = gato_solve(plan, G_val.data(), C_val.data(), g_val.data(), c_val.data(), lambda.data(),
-                                lam_out.data(), dz.data(), exit_tol, max_iters, warm, rho, &iters, &ms);
-            if (rc) { py::gil_scoped_acquire gil; check(rc); }
+            err.set(gato_solve(plan, G_val.data(), C_val.data(), g_val.data(), c_val.data(), lambda.data(),
+                               lam_out.data(), dz.data(), exit_tol, max_iters, warm, rho, &iters, &ms));
+            if (err.rc) return;
             total += ms;
             if (i == 0) { first_iters = iters; first_ms = ms; }
             g_cache.last_iters = iters;
         }
-    }
-    g_cache.first_ms = first_ms;
-    g_cache.avg_ms = (float)(total / testiters);
+        g_cache.first_ms = first_ms;
+        g_cache.avg_ms = avg_ms = (float)(total / testiters);
+    });
+    err.raise();
     if (!quiet()) {   // same two summary lines as gpu_library.cu:190,198 (log-scraping callers)
         std::printf("first run PCG terminated in %d iterations, time:  %f\n", first_iters, first_ms);
-        std::printf("avg time: %f\n", g_cache.avg_ms);
+        std::printf("avg time: %f\n", avg_ms);
         std::fflush(stdout);
     }
     py::list l, d;
@@ -125,12 +154,18 @@ py::tuple linsys_solve(std::vector<int> G_row, std::vector<int> G_col, std::vect
 }
 
 py::dict linsys_solve_info() {
+    int iters = -1, cl = 0, kpc = 0;
+    float first_ms = 0.f, avg_ms = 0.f;
+    bool have = false;
+    locked_nogil([&] {
+        iters = g_cache.last_iters; first_ms = g_cache.first_ms; avg_ms = g_cache.avg_ms;
+        have = g_cache.plan && gato_plan_get_cluster(g_cache.plan, &cl, &kpc) == GATO_OK;
+    });
     py::dict d;
-    d["iters"] = g_cache.last_iters;
-    d["first_ms"] = g_cache.first_ms;
-    d["avg_ms"] = g_cache.avg_ms;
-    int cl = 0, kpc = 0;
-    if (g_cache.plan && gato_plan_get_cluster(g_cache.plan, &cl, &kpc) == GATO_OK) {
+    d["iters"] = iters;
+    d["first_ms"] = first_ms;
+    d["avg_ms"] = avg_ms;
+    if (have) {
         d["cluster_ctas"] = cl;
         d["knots_per_cta"] = kpc;
     }
@@ -153,21 +188,22 @@ py::tuple linsys_solve_batched(iarr G_row, iarr G_col, farr G_val, iarr C_row, i
         throw py::value_error("leading dimensions must be nsys or 1 (shared)");
     std::vector<int> gr(G_row.data(), G_row.data() + G_row.size()), gc(G_col.data(), G_col.data() + G_col.size());
     std::vector<int> cr(C_row.data(), C_row.data() + C_row.size()), cc(C_col.data(), C_col.data() + C_col.size());
-    gato_plan* plan = plan_for(gr, gc, cr, cc);
     py::array_t<float> lam({nsys, kNl}), dz({nsys, kNz});
     py::array_t<int> iters(nsys);
     auto ld = [&](const farr& a) -> long long { return a.shape(0) == 1 && nsys > 1 ? 0 : (long long)a.shape(1); };
-    float ms = 0.f;
-    int rc;
-    {
-        py::gil_scoped_release nogil;
-        rc = gato_solve_batched(plan, nsys, G_val.data(), ld(G_val), C_val.data(), ld(C_val), g_val.data(),
-                                ld(g_val), c_val.data(), ld(c_val), nullptr, 0, lam.mutable_data(),
-                                dz.mutable_data(), iters.mutable_data(), exit_tol, max_iters, GATO_WARM_OFF,
-                                rho, &ms);
-    }
-    check(rc);
-    g_cache.avg_ms = g_cache.first_ms = ms;
+    const long long lG = ld(G_val), lC = ld(C_val), lg = ld(g_val), lc = ld(c_val);
+    const float *pG = G_val.data(), *pC = C_val.data(), *pg = g_val.data(), *pc = c_val.data();
+    float* pl_ = lam.mutable_data(); float* pd = dz.mutable_data(); int* pi = iters.mutable_data();
+    Err err;
+    locked_nogil([&] {
+        gato_plan* plan = plan_for(gr, gc, cr, cc, &err);
+        if (!plan) return;
+        float ms = 0.f;
+        err.set(gato_solve_batched(plan, nsys, pG, lG, pC, lC, pg, lg, pc, lc, nullptr, 0, pl_, pd, pi, exit_tol,
+                                   max_iters, GATO_WARM_OFF, rho, &ms));
+        g_cache.avg_ms = g_cache.first_ms = ms;
+    });
+    err.raise();
     return py::make_tuple(lam, dz, iters);
 }
 
@@ -188,25 +224,26 @@ py::tuple linsys_solve_blocks(farr G_dense, farr C_dense, farr g_val, farr c_val
     auto rows_ok = [&](const farr& a) { return a.shape(0) == nsys || a.shape(0) == 1; };
     if (!rows_ok(G_dense) || !rows_ok(C_dense) || !rows_ok(c_val))
         throw py::value_error("leading dimensions must be nsys or 1 (shared)");
-    if (!g_block_plan) {
-        int dev = 0;
-        if (const char* d = std::getenv("GATO_B200_DEVICE")) dev = std::atoi(d);
-        check(gato_plan_create_blocks(kS, kC, kK, dev, 1, &g_block_plan));
-    }
     py::array_t<float> lam({nsys, kNl}), dz({nsys, kNz});
     py::array_t<int> iters(nsys);
     auto ld = [&](const farr& a) -> long long { return a.shape(0) == 1 && nsys > 1 ? 0 : (long long)a.shape(1); };
-    float ms = 0.f;
-    int rc;
-    {
-        py::gil_scoped_release nogil;
-        rc = gato_solve_batched(g_block_plan, nsys, G_dense.data(), ld(G_dense), C_dense.data(), ld(C_dense),
-                                g_val.data(), ld(g_val), c_val.data(), ld(c_val), nullptr, 0, lam.mutable_data(),
-                                dz.mutable_data(), iters.mutable_data(), exit_tol, max_iters, GATO_WARM_OFF, rho,
-                                &ms);
-    }
-    check(rc);
-    g_cache.avg_ms = g_cache.first_ms = ms;
+    const long long lG = ld(G_dense), lC = ld(C_dense), lg = ld(g_val), lc = ld(c_val);
+    const float *pG = G_dense.data(), *pC = C_dense.data(), *pg = g_val.data(), *pc = c_val.data();
+    float* pl_ = lam.mutable_data(); float* pd = dz.mutable_data(); int* pi = iters.mutable_data();
+    Err err;
+    locked_nogil([&] {
+        if (!g_block_plan) {
+            int dev = 0;
+            if (const char* d = std::getenv("GATO_B200_DEVICE")) dev = std::atoi(d);
+            err.set(gato_plan_create_blocks(kS, kC, kK, dev, 1, &g_block_plan));
+            if (err.rc) { g_block_plan = nullptr; return; }
+        }
+        float ms = 0.f;
+        err.set(gato_solve_batched(g_block_plan, nsys, pG, lG, pC, lC, pg, lg, pc, lc, nullptr, 0, pl_, pd, pi,
+                                   exit_tol, max_iters, GATO_WARM_OFF, rho, &ms));
+        g_cache.avg_ms = g_cache.first_ms = ms;
+    });
+    err.raise();
     return py::make_tuple(lam, dz, iters);
 }
 
@@ -225,22 +262,23 @@ py::tuple linsys_solve_sequence(iarr G_row, iarr G_col, farr G_val, iarr C_row, 
         throw py::value_error("leading dimensions must be T or 1 (shared); rho must have T entries");
     std::vector<int> gr(G_row.data(), G_row.data() + G_row.size()), gc(G_col.data(), G_col.data() + G_col.size());
     std::vector<int> cr(C_row.data(), C_row.data() + C_row.size()), cc(C_col.data(), C_col.data() + C_col.size());
-    gato_plan* plan = plan_for(gr, gc, cr, cc);
     py::array_t<float> lam({T, kNl}), dz({T, kNz});
     py::array_t<int> iters(T);
     auto ld = [&](const farr& a) -> long long { return a.shape(0) == 1 && T > 1 ? 0 : (long long)a.shape(1); };
-    float ms = 0.f;
-    int rc;
-    {
-        py::gil_scoped_release nogil;
-        rc = gato_solve_sequence(plan, T, G_val.data(), ld(G_val), C_val.data(), ld(C_val), g_val.data(),
-                                 ld(g_val), c_val.data(), ld(c_val), rho.data(), 0.f, nullptr,
-                                 lam.mutable_data(), dz.mutable_data(), iters.mutable_data(), exit_tol, max_iters,
-                                 warm_start ? GATO_WARM_TRUE : GATO_WARM_OFF, &ms);
-    }
-    check(rc);
-    g_cache.avg_ms = ms / (float)T;
-    g_cache.first_ms = ms;
+    const long long lG = ld(G_val), lC = ld(C_val), lg = ld(g_val), lc = ld(c_val);
+    const float *pG = G_val.data(), *pC = C_val.data(), *pg = g_val.data(), *pc = c_val.data(), *pr = rho.data();
+    float* pl_ = lam.mutable_data(); float* pd = dz.mutable_data(); int* pi = iters.mutable_data();
+    Err err;
+    locked_nogil([&] {
+        gato_plan* plan = plan_for(gr, gc, cr, cc, &err);
+        if (!plan) return;
+        float ms = 0.f;
+        err.set(gato_solve_sequence(plan, T, pG, lG, pC, lC, pg, lg, pc, lc, pr, 0.f, nullptr, pl_, pd, pi, exit_tol,
+                                    max_iters, warm_start ? GATO_WARM_TRUE : GATO_WARM_OFF, &ms));
+        g_cache.avg_ms = ms / (float)T;
+        g_cache.first_ms = ms;
+    });
+    err.raise();
     return py::make_tuple(lam, dz, iters);
 }
 
@@ -256,6 +294,10 @@ PYBIND11_MODULE(gpu_library, m) {
     m.def("linsys_solve_batched", &linsys_solve_batched);
     m.def("linsys_solve_blocks", &linsys_solve_blocks);
     m.def("linsys_solve_sequence", &linsys_solve_sequence);
-    m.def("set_true_warm_start", [](bool on) { g_cache.true_warm = on; });
-    m.def("set_cluster", [](int cl) { if (g_cache.plan) check(gato_plan_set_cluster(g_cache.plan, cl)); });
+    m.def("set_true_warm_start", [](bool on) { locked_nogil([&] { g_cache.true_warm = on; }); });
+    m.def("set_cluster", [](int cl) {
+        Err err;
+        locked_nogil([&] { if (g_cache.plan) err.set(gato_plan_set_cluster(g_cache.plan, cl)); });
+        err.raise();
+    });
 }

@@ -15,12 +15,14 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgato_b200.so")
 
 WARM_OFF, WARM_REFERENCE, WARM_TRUE, WARM_RESIDENT = 0, 1, 2, 3
+PRECOND_STAIR, PRECOND_BLOCK_JACOBI = 0, 1
 
 #: every symbol include/gato_b200.h declares
 SYMBOLS = [
     "gato_supported_sizes", "gato_last_error", "gato_device_count", "gato_plan_create",
     "gato_plan_create_blocks", "gato_solve_sequence",
     "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel", "gato_plan_set_pipeline", "gato_plan_set_staging", "gato_plan_set_zero_copy",
+    "gato_plan_set_preconditioner", "gato_plan_get_preconditioner",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -60,6 +62,8 @@ def lib():
     L.gato_plan_set_pipeline.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_staging.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_zero_copy.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_set_preconditioner.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_get_preconditioner.argtypes = [C.c_void_p]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
     L.gato_solve.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_int,
                              C.c_float, _ip, _fp]
@@ -173,6 +177,15 @@ class Plan:
     def set_zero_copy(self, on):
         """solve(): staged kernels read the pinned input buffer in place over PCIe (default on); same results."""
         _check(lib().gato_plan_set_zero_copy(self._h, int(bool(on))))
+
+    def set_preconditioner(self, which):
+        """PRECOND_STAIR (default, the reference as shipped: iteration counts match it) or PRECOND_BLOCK_JACOBI
+        (the reference's SS_PRECON = 0, include/gato_defines.h:9-10: theta^-1 blocks only)."""
+        which = {"stair": PRECOND_STAIR, "block_jacobi": PRECOND_BLOCK_JACOBI}.get(which, which)
+        _check(lib().gato_plan_set_preconditioner(self._h, int(which)))
+
+    def preconditioner(self):
+        return int(lib().gato_plan_get_preconditioner(self._h))
 
     def cluster(self):
         a, b = C.c_int(), C.c_int()

@@ -92,6 +92,21 @@ int gato_plan_get_kernel(const gato_plan* plan);
  * (src/gato_schur.cuh:674-743). */
 int gato_plan_set_staging(gato_plan* plan, int on);
 
+/* Preconditioner of the PCG loop.  The reference selects it at compile time (include/gato_defines.h:9-11:
+ * BLOCK_J_PRECON, SS_PRECON, PRECONDITIONER_BANDWIDTH "must be set for compile"; consulted at
+ * src/gato_schur.cuh:407-429 and :496, :965) and ships 1 / 1 / 3 = the symmetric stair preconditioner, the only
+ * setting for which it initialises every block of d_Pinv it reads.  Here it is a plan switch:
+ *   GATO_PRECOND_STAIR         P^-1 = D^-1 - D^-1 O D^-1 (default; the parity mode -- iteration counts match the
+ *                              reference build)
+ *   GATO_PRECOND_BLOCK_JACOBI  P^-1 = D^-1 = diag(theta_b^-1): what SS_PRECON = 0 intends (gato_form_ss not run,
+ *                              off-diagonal blocks of Pinv taken as zero).  More iterations, each with one
+ *                              exchange + barrier and 6 S^2 multiply-adds per knot less.  Same solution within the
+ *                              exit tolerance; iteration counts differ from the reference build by design. */
+#define GATO_PRECOND_STAIR 0
+#define GATO_PRECOND_BLOCK_JACOBI 1
+int gato_plan_set_preconditioner(gato_plan* plan, int preconditioner);
+int gato_plan_get_preconditioner(const gato_plan* plan);
+
 /* gato_solve only: when the kernel stages its inputs with TMA, let those bulk copies read the plan's pinned
  * host staging buffer in place over PCIe instead of copying it to the device first (default on).  Removes
  * one of the two DMA operations of the reference's bracket (the H2D of gpu_library.cu:150-157).  Same results. */
