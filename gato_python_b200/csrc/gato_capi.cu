@@ -14,6 +14,7 @@
 #include "../../include/gato_b200.h"
 #include "gato_kernels.cuh"
 #include "gato_kernel_v2.cuh"
+#include "gato_kernel_v5.cuh"
 
 #ifndef GATO_EXTRA_S
 #define GATO_EXTRA_S 0
@@ -86,7 +87,8 @@ struct gato_plan {
     int S, C, K, nnzG, nnzC, device, max_batch;
     int n_z, n_l, g_dense, c_dense;
     int cl_override = 0;
-    int kernel = 0;         // 0 = automatic, 1 = cluster kernel (v1), 2 = one-CTA-per-system kernel (v2)
+    int kernel = 0;         // 0 = automatic, 1 = cluster kernel (v1), 2 = one-CTA-per-system kernel (v2), 3 / 4 = v2 over a
+                            // cluster / a cooperative grid, 5 = scaled system in two kernels
     int g_diag = 0;         // G's pattern is purely diagonal
     int sm_count = 0;
     int smem_optin = 0;
@@ -102,6 +104,13 @@ struct gato_plan {
     // device: staged inputs / outputs for the host-buffer entry points
     DevBuf dG, dC, dg, dc, dl, dlo, ddz, dit, dbg;
     DevBuf dgrid;           // kernel 4: global scratch of the cooperative-grid variant
+    // kernel 5: per-system scratch between its two kernels (ScaledLayout), one chunk of systems -- one buffer per
+    // stream the plan has been used on (launches on different streams may overlap; the chunk pipeline uses four)
+    static constexpr int kScr = 8;
+    DevBuf dscr[kScr];
+    cudaStream_t scr_stream[kScr] = {};
+    int nscr = 0;
+    int v5_chunk = 0;       // kernel 5: systems per chunk (0 = automatic)
     PinBuf hin, hout;   // pinned staging for the single-solve path
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -114,6 +123,8 @@ struct gato_plan {
     // one-CTA kernel: resident CTAs per SM for the shared-memory size this plan launches with (computed once per
     // size; per plan, not per process: plans of different horizons / devices do not disturb each other)
     mutable int occ_smem = -1, occ_val = 0;
+    mutable int occ5_smem = -1, occ5_val = 0;   // the same for the first half of kernel 5
+    mutable int occp_val = 0;                   // second half of kernel 5: resident CTAs per SM
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -207,10 +218,12 @@ int v2_pick_nt(const gato_plan* pl) {   // smallest menu entry that holds K knot
     return 0;
 }
 
-template <int S, int C, int NT>
+template <int S, int C, int NT, bool SCALED = false>
 int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     using L = gato::Layout2<S, C>;
-    auto kern = gato::gato_fused_solve_v2<S, C, NT>;
+    auto kern = gato::gato_fused_solve_v2<S, C, NT, false, false, SCALED>;
+    int& occ_smem = SCALED ? pl->occ5_smem : pl->occ_smem;
+    int& occ_val = SCALED ? pl->occ5_val : pl->occ_val;
     const int core = L::smem_floats(q.p.K, NT);
     // TMA staging of the C / G / g values (+ 16 bytes for the mbarrier) when it fits beside the system
     const int stage = gato::stage_len(q.nnzC) + gato::stage_len(q.nnzG) + gato::stage_len(pl->n_z);
@@ -234,14 +247,14 @@ int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
             raised[di] = true;
         }
     }
-    if (pl->occ_smem != (int)smem) {
+    if (occ_smem != (int)smem) {
         int occ = 0;
         GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
         if (occ < 1) return fail(GATO_EUNSUPPORTED, "one-CTA kernel does not fit an SM (%zu B shared memory)", smem);
-        pl->occ_smem = (int)smem;
-        pl->occ_val = occ;
+        occ_smem = (int)smem;
+        occ_val = occ;
     }
-    const int resident = pl->occ_val * (pl->sm_count > 0 ? pl->sm_count : 148);
+    const int resident = occ_val * (pl->sm_count > 0 ? pl->sm_count : 148);
     const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
     kern<<<grid, NT, smem, st>>>(q);
     GATO_CUDA(cudaGetLastError());
@@ -257,6 +270,111 @@ int launch_v2_sc(const gato_plan* pl, const gato::SolveParams2& q, cudaStream_t 
         if (nt == V2Menu<S>::nt[2]) return launch_v2_t<S, C, V2Menu<S>::nt[2]>(pl, q, st);
     }
     return fail(GATO_EUNSUPPORTED, "K=%d does not fit the one-CTA kernel", pl->K);
+}
+
+// ---- kernel 5: the scaled system in two kernels (gato_kernel_v5.cuh) -------------------------------------------
+// first half = the one-CTA kernel's unpack + Schur phases + the FP64 congruence (1 CTA per SM, 255 registers), second
+// half = PCG on S^ = I + O^ + dz (2 CTAs per SM); they meet in a per-plan scratch buffer that holds one chunk of
+// systems (ScaledLayout::KSCR floats per knot) and is reused chunk after chunk, so it stays in the 126 MB L2.
+template <int S> struct HasV5 { static constexpr bool value = (S == 14); };
+constexpr int kV5Threads = 224;
+
+template <int S, int C>
+int v5_ok_sc(const gato_plan* pl) {
+    if constexpr (HasV5<S>::value) {
+        using L = gato::Layout2<S, C>;
+        return (L::LPK * pl->K <= kV5Threads && v2_pick_nt<S, C>(pl) > 0) ? 1 : 0;
+    } else {
+        return 0;
+    }
+}
+
+template <int S, int C>
+long long v5_scratch_per_system(const gato_plan* pl) {
+    if constexpr (HasV5<S>::value) return (long long)pl->K * gato::ScaledLayout<S, C>::KSCR;
+    else return 0;
+}
+
+gato::SolveParams slice_params(const gato::SolveParams& base, int r0, int nr) {
+    gato::SolveParams p = base;
+    p.nsys = nr;
+    p.G_val = base.G_val + (long long)r0 * base.ldG;
+    p.C_val = base.C_val + (long long)r0 * base.ldC;
+    p.g = base.g + (long long)r0 * base.ldg;
+    p.c = base.c + (long long)r0 * base.ldc;
+    if (base.lambda_in) p.lambda_in = base.lambda_in + (long long)r0 * base.ldl;
+    p.lambda_out = base.lambda_out + (long long)r0 * base.ldlo;
+    p.dz_out = base.dz_out + (long long)r0 * base.lddz;
+    p.iters_out = base.iters_out + r0;
+    if (base.eta_out) p.eta_out = base.eta_out + r0;
+    return p;
+}
+
+template <int S, int C>
+int launch_v5_first(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
+    if constexpr (HasV5<S>::value) {
+        const int nt = v2_pick_nt<S, C>(pl);
+        if (nt == V2Menu<S>::nt[0]) return launch_v2_t<S, C, V2Menu<S>::nt[0], true>(pl, q, st);
+        if (nt == V2Menu<S>::nt[1]) return launch_v2_t<S, C, V2Menu<S>::nt[1], true>(pl, q, st);
+        if constexpr (V2Menu<S>::n > 2) {
+            if (nt == V2Menu<S>::nt[2]) return launch_v2_t<S, C, V2Menu<S>::nt[2], true>(pl, q, st);
+        }
+    }
+    return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
+}
+
+template <int S, int C>
+int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
+    if constexpr (HasV5<S>::value) {
+        using L = gato::Layout2<S, C>;
+        constexpr int NT = kV5Threads, NKP = (NT / 32) * L::KPW;
+        constexpr size_t smem = (size_t)(4 * (NKP + 2) * L::VS + NKP * (L::VS + L::LDC) + 64) * sizeof(float);
+        auto kern = gato::gato_pcg_scaled<S, C, NT>;
+        if (pl->occp_val == 0) {
+            int occ = 0;
+            GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+            if (occ < 1) return fail(GATO_EUNSUPPORTED, "second half of kernel 5 does not fit an SM");
+            pl->occp_val = occ;
+        }
+        const int resident = pl->occp_val * (pl->sm_count > 0 ? pl->sm_count : 148);
+        const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
+        kern<<<grid, NT, smem, st>>>(q);
+        GATO_CUDA(cudaGetLastError());
+        return GATO_OK;
+    }
+    return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
+}
+
+// first_only: run just the first half on the first system and leave its scratch in pl->dscr (parity hook)
+template <int S, int C>
+int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool first_only) {
+    if (!v5_ok_sc<S, C>(pl)) return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
+    if (q.p.warm == 2)
+        return fail(GATO_EUNSUPPORTED, "kernel 5 has no true warm start yet (use kernel 2 for GATO_WARM_TRUE)");
+    const long long per = v5_scratch_per_system<S, C>(pl);
+    const int sms = pl->sm_count > 0 ? pl->sm_count : 148;
+    int chunk = pl->v5_chunk > 0 ? pl->v5_chunk : 2 * sms;
+    if (chunk > q.p.nsys) chunk = q.p.nsys;
+    int si = 0;
+    while (si < pl->nscr && pl->scr_stream[si] != st) ++si;
+    if (si == pl->nscr) {
+        if (pl->nscr == gato_plan::kScr)
+            return fail(GATO_EUNSUPPORTED, "kernel 5 keeps one scratch buffer per stream: more than %d streams on one plan", gato_plan::kScr);
+        pl->scr_stream[pl->nscr++] = st;
+    }
+    GATO_CUDA(pl->dscr[si].ensure((size_t)chunk * (size_t)per * sizeof(float)));
+    q.scr = (float*)pl->dscr[si].p;
+    q.scr_ld = per;
+    const gato::SolveParams base = q.p;
+    for (int r0 = 0; r0 < base.nsys; r0 += chunk) {
+        const int nr = base.nsys - r0 < chunk ? base.nsys - r0 : chunk;
+        q.p = slice_params(base, r0, nr);
+        int rc = launch_v5_first<S, C>(pl, q, st);
+        if (rc || first_only) return rc;
+        if ((rc = launch_v5_second<S, C>(pl, q, st))) return rc;
+    }
+    return GATO_OK;
 }
 
 // ---- v2 over a thread-block cluster (kernel 3): horizons beyond one SM's registers ---------------------
@@ -485,8 +603,25 @@ int v2_nt_for(const gato_plan* pl) {
 }
 
 bool use_v2(const gato_plan* pl) {
-    if (pl->kernel == 1 || pl->kernel == 3 || pl->kernel == 4 || (pl->kernel == 0 && pl->cl_override > 0)) return false;
+    if (pl->kernel == 1 || pl->kernel == 3 || pl->kernel == 4 || pl->kernel == 5 || (pl->kernel == 0 && pl->cl_override > 0))
+        return false;
     return v2_nt_for(pl) > 0;
+}
+
+bool v5_ok(const gato_plan* pl) {
+#define X(s, c) if (pl->S == s && pl->C == c) return v5_ok_sc<s, c>(pl) != 0;
+    GATO_FOR_SIZES(X)
+#undef X
+    return false;
+}
+
+bool use_v5(const gato_plan* pl) { return pl->kernel == 5 && v5_ok(pl); }
+
+long long v5_scratch_floats(const gato_plan* pl) {
+#define X(s, c) if (pl->S == s && pl->C == c) return v5_scratch_per_system<s, c>(pl);
+    GATO_FOR_SIZES(X)
+#undef X
+    return 0;
 }
 
 int v2cl_cfg_for(const gato_plan* pl, ClusterCfg* cfg) {
@@ -558,6 +693,17 @@ int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_
     return fail(GATO_EUNSUPPORTED, "no v2 kernels for S=%d C=%d", pl->S, pl->C);
 }
 
+int launch_solve_v5(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st, bool first_only = false) {
+    gato::SolveParams2 q = {};
+    q.p = p;
+    q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
+#define X(s, c) if (pl->S == s && pl->C == c) return launch_v5_sc<s, c>(pl, q, st, first_only);
+    GATO_FOR_SIZES(X)
+#undef X
+    return fail(GATO_EUNSUPPORTED, "no kernel 5 for S=%d C=%d", pl->S, pl->C);
+}
+
 int launch_solve_v2cl(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
     gato::SolveParams2 q;
     q.p = p;
@@ -590,6 +736,7 @@ int launch_solve_v2grid(gato_plan* pl, const gato::SolveParams& p, cudaStream_t 
 
 // the kernel the plan selects; dumps of the Schur intermediates exist only in the cluster kernel
 int launch_auto(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
+    if (p.dbg_S == nullptr && use_v5(pl)) return launch_solve_v5(pl, p, st);
     if (p.dbg_S == nullptr && use_v2(pl)) return launch_solve_v2(pl, p, st);
     if (p.dbg_S == nullptr && use_v2cl(pl)) return launch_solve_v2cl(pl, p, st);
     if (p.dbg_S == nullptr && use_v2grid(pl)) return launch_solve_v2grid(pl, p, st);

@@ -90,6 +90,34 @@ struct Layout2 {
     }
 };
 
+// Kernel 5: what its first half (Schur + congruence, FP64) hands to its second half (PCG + dz) through global memory,
+// per knot, in floats.  [0, REG): verbatim copy of the knot's shared-memory region A | B | Q^-1 | R^-1 | q | r (the dz
+// phase reads it with the same offsets); PSI: psi_b = M_b phi_b M_{b-1}^T in lane-ready order (LPK lanes x PSIL floats:
+// lane (g, h) holds rows g*R + rp_h(i) x columns h*HALFU + cp_g(j), rp / cp = the half-swap permutation when the flag
+// is set, so that both reduce-scatters of the PCG loop are select-free); M: M_b row-major [S][VS] in pos layout (the
+// final lambda = M^T lambda^); GAM: gamma^_b in pos layout.
+template <int S, int C>
+struct ScaledLayout {
+    using L = Layout2<S, C>;
+    static constexpr int REG = L::oPhi;
+    static constexpr int PSIL = (L::R * L::HALFU + 3) & ~3;
+    static constexpr int oPSI = REG;
+    static constexpr int oM = oPSI + L::LPK * PSIL;
+    static constexpr int oGAM = oM + S * L::VS;
+    static constexpr int KSCR = oGAM + L::VS;
+    // FP64 scratch inside a knot's (dead) shared-memory region: M64 [S][S] doubles, then T64 [S][2 HT] doubles
+    static constexpr int HT = (L::HALFU + 1) & ~1;
+    static constexpr int oM64 = 0, oT64 = 2 * S * S;
+    static_assert(L::H == 2 && L::LPK == 4, "kernel 5 is written for the 2 x 2 lane split (even S > 8)");
+    static_assert(oT64 + 2 * S * 2 * HT <= L::KN0, "FP64 scratch must fit the knot region");
+    static_assert(REG % 4 == 0 && KSCR % 4 == 0, "16-byte aligned sections");
+    // the half-swap permutation of R rows (or HALFU columns): [OWN .. R) first, so that the rows a lane keeps and the
+    // rows it sends in a reduce-scatter sit in the same registers for both lanes of a pair
+    __host__ __device__ static constexpr int hswap(int i) {
+        return (i + L::OWN < L::R) ? i + L::OWN : (i >= L::OWN ? i - L::OWN : i);
+    }
+};
+
 // row maps for the in-register Gauss-Jordan: which lane-in-knot / register holds row r
 template <int S, int C>
 struct MapState {
@@ -185,6 +213,8 @@ struct SolveParams2 {
     int kpc;              // cluster variant: knots owned per CTA (local slots 1..kpc; 0 and kpc+1 are halos)
     int ncta;             // grid variant: CTAs per system
     float* gbuf;          // grid variant: global scratch, [2][256] per-CTA dot partials | [ncta][3][2][VS] boundary slices
+    float* scr;           // kernel 5 (scaled system): per-system scratch between its two kernels (ScaledLayout)
+    long long scr_ld;     // floats between consecutive systems in scr
 };
 
 // ---- TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier) ---------------------
@@ -266,9 +296,15 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // 16-CTA cluster (the job of the reference's grid-stride parallelPCG_fixed, src/gato_pcg.cuh:17-268).  The CTAs are
 // not cluster mates, so boundary slices and per-CTA dot partials travel through a small global scratch buffer and
 // the synchronisation points are grid.sync(); every CTA reduces the same partials in the same order.
-template <int S, int C, int NT, bool CL = false, bool GRID = false>
+//
+// SCALED = true: FIRST HALF OF KERNEL 5 (gato_kernel_v5.cuh).  The same unpack and Schur phases, then -- instead of
+// the PCG loop -- the congruence  S^ = M S M^T  with M_b = inverse Cholesky factor of theta_b, formed in FP64, whose
+// diagonal blocks are the identity: only psi_b = M_b phi_b M_{b-1}^T, gamma^ = M gamma and M leave the SM (to the
+// per-system scratch q.scr), together with a verbatim copy of the knot regions for the dz phase of the second half.
+template <int S, int C, int NT, bool CL = false, bool GRID = false, bool SCALED = false>
 __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 q) {
     static_assert(!GRID || CL, "the grid variant uses the cluster variant's decomposition");
+    static_assert(!SCALED || !CL, "the scaled-system variant is a one-CTA kernel");
     using L = Layout2<S, C>;
     using MS = MapState<S, C>;
     using MC = MapControl<S, C>;
@@ -538,7 +574,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0.
             // A persistent CTA's later systems with a purely diagonal G write exactly the words its first system
             // wrote in the knot regions (same pattern, reciprocals in place): only the iterates need clearing.
-            const bool keep_regions = !CL && q.g_diag && sys >= (int)gridDim.x;
+            const bool keep_regions = !CL && !SCALED && q.g_diag && sys >= (int)gridDim.x;   // (kernel 5 reuses the regions as FP64 scratch)
             float4* s4 = reinterpret_cast<float4*>(smem);
             for (int i = (keep_regions ? nreg * KN / 4 : 0) + tid; i < nfloats / 4; i += NT)
                 s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -829,7 +865,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 #pragma unroll
                     for (int j = 0; j < S; ++j) th[i][j] = a[i][j];
             }
-            gj_invert_knot<MS, LPK>(a, lik, lane);
+            if (!(SCALED && pass == 1)) gj_invert_knot<MS, LPK>(a, lik, lane);   // kernel 5 never needs theta^-1
             if (pass == 0) {
                 if (inv) {
 #pragma unroll
@@ -867,6 +903,9 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         stamp(p, 4);
         __syncthreads();   // phi_b of every block row is in shared memory
 
+        if constexpr (SCALED) {
+#include "gato_kernel_v5_schur.inc"
+        } else {
         // ==== 4. iteration matrices into registers, matrix mapping ====================================
         // Lane (g, h) holds rows g*R .. g*R+R-1 of [S_left | S_main | S_right] restricted to its column
         // group, and the same rows of theta^-1.  Local column order (H == 2): [side knot (VS positions:
@@ -1332,6 +1371,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             p.iters_out[sys] = iters;
             if (p.eta_out != nullptr) p.eta_out[sys] = fabsf(eta_last);
         }
+        }   // !SCALED
+        sys = ctl[0];
         __syncthreads();   // dz has read the knot regions and the iterates: the next system may clear them
         if (tid == 0) {
             ctl[0] = sys + (int)gridDim.x / ncta;

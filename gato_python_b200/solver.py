@@ -23,6 +23,7 @@ SYMBOLS = [
     "gato_plan_create_blocks", "gato_solve_sequence",
     "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel", "gato_plan_set_pipeline", "gato_plan_set_staging", "gato_plan_set_zero_copy",
     "gato_plan_set_preconditioner", "gato_plan_get_preconditioner",
+    "gato_scaled_layout", "gato_scaled_debug", "gato_plan_set_scaled_chunk",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -64,6 +65,9 @@ def lib():
     L.gato_plan_set_zero_copy.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_preconditioner.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_get_preconditioner.argtypes = [C.c_void_p]
+    L.gato_scaled_layout.argtypes = [C.c_void_p, _ip]
+    L.gato_scaled_debug.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, C.c_float, _fp, _ll]
+    L.gato_plan_set_scaled_chunk.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
     L.gato_solve.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_int,
                              C.c_float, _ip, _fp]
@@ -186,6 +190,37 @@ class Plan:
 
     def preconditioner(self):
         return int(lib().gato_plan_get_preconditioner(self._h))
+
+    def set_scaled_chunk(self, systems_per_chunk):
+        """Kernel 5: systems per pass through its scratch buffer (0 = automatic)."""
+        _check(lib().gato_plan_set_scaled_chunk(self._h, int(systems_per_chunk)))
+
+    def scaled_debug(self, G_val, C_val, g, c, rho):
+        """Kernel 5, first half only, one system: -> dict(psi [K, S, S] (psi_b = M_b phi_b M_{b-1}^T, block 0 zero),
+        M [K, S, S], gamma_hat [K, S], region [K, REG]) decoded from the scratch layout."""
+        lay = (C.c_int * 8)()
+        _check(lib().gato_scaled_layout(self._h, lay))
+        KSCR, REG, oPSI, PSIL, oM, oGAM, VS, HALFP = list(lay)
+        S, K = self.S, self.K
+        raw = np.zeros(K * KSCR, np.float32)
+        G_val = _f32(G_val, (self.nnzG,)); C_val = _f32(C_val, (self.nnzC,))
+        g = _f32(g, (self.n_z,)); c = _f32(c, (self.n_l,))
+        _check(lib().gato_scaled_debug(self._h, _f(G_val), _f(C_val), _f(g), _f(c), float(rho), _f(raw), raw.size))
+        raw = raw.reshape(K, KSCR)
+        HU = S // 2
+        pos = [(r // HU) * HALFP + r % HU for r in range(S)]
+        M = raw[:, oM:oM + S * VS].reshape(K, S, VS)[:, :, pos]
+        gam = raw[:, oGAM:oGAM + VS][:, pos]
+        OWN = (HU + 1) // 2
+        hs = [i + OWN if i + OWN < HU else (i - OWN if i >= OWN else i) for i in range(HU)]
+        psi = np.zeros((K, S, S), np.float32)
+        for lik in range(4):
+            gg, hh = lik // 2, lik % 2
+            blk = raw[:, oPSI + lik * PSIL: oPSI + lik * PSIL + HU * HU].reshape(K, HU, HU)
+            for i in range(HU):
+                for j in range(HU):
+                    psi[:, gg * HU + (hs[i] if hh else i), hh * HU + (hs[j] if gg else j)] = blk[:, i, j]
+        return dict(psi=psi, M=M, gamma_hat=gam, region=raw[:, :REG])
 
     def cluster(self):
         a, b = C.c_int(), C.c_int()

@@ -176,6 +176,22 @@ int gato_solve_batched_device(gato_plan* plan, int nsys,
 int gato_unpack(gato_plan* plan, const float* G_val, const float* C_val, float rho,
                 float* G_dense_out, float* C_dense_out);
 
+/* Kernel 5 ("scaled system", gato_plan_set_kernel(plan, 5); STATE_SIZE = 14, K <= 56): the hot path as TWO kernels.
+ * The first forms the reference's Schur blocks theta_b, phi_b, gamma_b (src/gato_schur.cuh:13-494) and, in FP64, the
+ * congruence S^ = M S M^T (theta_b = L_b L_b^T, M_b = L_b^-1) whose diagonal blocks are the identity; the second runs
+ * the reference's PCG (src/gato_pcg.cuh:300-437, same update order, exit rule and iteration numbering) on
+ * S^ = I + O^ with P^^-1 = I - O^ -- the stair preconditioner (src/gato_schur.cuh:498-649) in those coordinates -- and
+ * recovers lambda = M^T lambda^ and dz (src/gato_schur.cuh:758-879).  Identical iterates in exact arithmetic; one
+ * 7 x 7 block of psi_b = M_b phi_b M_{b-1}^T per lane instead of 196 matrix words, two systems resident per SM.
+ * gato_scaled_layout: {floats per knot, region copy, psi offset, psi floats per lane, M offset, gamma^ offset, VS,
+ * HALFP} of the per-knot scratch; gato_scaled_debug: run the first kernel on one system and return its scratch
+ * (parity hook for psi, M, gamma^); gato_plan_set_scaled_chunk: systems per pass through the scratch buffer
+ * (0 = automatic: two per SM, which keeps the scratch in L2). */
+int gato_scaled_layout(const gato_plan* plan, int* layout8);
+int gato_scaled_debug(gato_plan* plan, const float* G_val, const float* C_val, const float* g, const float* c,
+                      float rho, float* scratch_out, long long nfloats);
+int gato_plan_set_scaled_chunk(gato_plan* plan, int systems_per_chunk);
+
 /* Solve one system and also return the Schur-phase intermediates in the reference's device layout
  * and (negated) storage signs: S_out, Pinv_out 3*S^2*K floats (gpu_library.cu:40-41), gamma_out
  * S*K floats, Ginv_out (S^2+C^2)K-C^2 floats (what form_schur leaves in d_G_dense,

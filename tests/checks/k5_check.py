@@ -1,0 +1,62 @@
+"""Kernel 5 (scaled system, two kernels) against kernel 2 on the benchmark batch: parity of the two and device time
+per 8192 resident systems, per half of kernel 5 and for a few chunk sizes.  GPU box only."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from gato_python_b200 import Plan  # noqa: E402
+from gato_python_b200.problems import iiwa_like_batch_fast  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+b = iiwa_like_batch_fast(n, 14, 7, 50, seed=1000)
+dev = torch.device("cuda", 0)
+pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
+d = {k: torch.from_numpy(b[k]).to(dev) for k in ("G_val", "C_val", "g", "c")}
+nnzG, nnzC = b["G_val"].shape[1], b["C_val"].shape[1]
+st = torch.cuda.current_stream()
+out = {}
+res = {}
+
+
+def run(lam, dz, its):
+    pl.solve_batched_device(n, d["G_val"].data_ptr(), nnzG, d["C_val"].data_ptr(), nnzC, d["g"].data_ptr(), pl.n_z,
+                            d["c"].data_ptr(), pl.n_l, lam.data_ptr(), dz.data_ptr(), its.data_ptr(),
+                            exit_tol=b["exit_tol"], max_iters=b["max_iters"], rho=b["rho"], stream=st.cuda_stream)
+
+
+for kernel, chunk in ((2, 0), (5, 0), (5, 148), (5, 592), (5, 1184), (5, 2368), (5, 8192)):
+    pl.set_kernel(kernel)
+    if kernel == 5:
+        pl.set_scaled_chunk(chunk)
+    lam = torch.zeros((n, pl.n_l), device=dev); dz = torch.zeros((n, pl.n_z), device=dev)
+    its = torch.zeros(n, dtype=torch.int32, device=dev)
+    for _ in range(3):
+        run(lam, dz, its)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    e0.record()
+    for _ in range(reps):
+        run(lam, dz, its)
+    e1.record(); e1.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    key = f"k{kernel}_chunk{chunk}"
+    out[key] = {"ms_per_batch": ms, "solves_per_s": n / ms * 1e3, "mean_iters": float(its.float().mean())}
+    res[key] = (lam.cpu().numpy(), dz.cpu().numpy(), its.cpu().numpy())
+    print(key, out[key], flush=True)
+
+l2, z2, i2 = res["k2_chunk0"]
+l5, z5, i5 = res["k5_chunk0"]
+rl = np.linalg.norm(l5 - l2, axis=1) / np.linalg.norm(l2, axis=1)
+rz = np.linalg.norm(z5 - z2, axis=1) / np.linalg.norm(z2, axis=1)
+out["k5_vs_k2"] = {"max_rel_lambda": float(rl.max()), "mean_rel_lambda": float(rl.mean()), "max_rel_dz": float(rz.max()),
+                   "iter_diff_hist": {int(k): int(v) for k, v in zip(*np.unique(i5.astype(int) - i2.astype(int), return_counts=True))},
+                   "nan": bool(np.isnan(l5).any())}
+for key in ("k5_chunk148", "k5_chunk8192"):
+    out[key]["bitwise_equal_to_default_chunk"] = bool(np.array_equal(res[key][0], l5) and np.array_equal(res[key][2], i5))
+print(json.dumps(out))

@@ -225,3 +225,129 @@ def test_config5_full_length_cold_and_warm():
     for t0 in (200, 400, 600, 800, 990):
         chained(t0, t0 + 10, lam_w[t0 - 1])
     pl.close()
+
+
+# ---- kernel 5: the scaled system S^ = M S M^T in two kernels (gato_kernel_v5.cuh) -----------------------------------
+def _scaled_reference(prob):
+    """FP64 restatement of the first half of kernel 5 from the oracle's FP32 Schur blocks (theta, phi, gamma as the
+    reference forms them): M_b = inverse Cholesky factor of theta_b, psi_b = M_b phi_b M_{b-1}^T, gamma^ = M gamma."""
+    _, _, io = oracle(prob)
+    sch = io["schur"]
+    theta = (-sch["S_st"][:, 1]).astype(np.float64)
+    phi = (-sch["S_st"][:, 0]).astype(np.float64)
+    gam = (-sch["gamma_st"]).reshape(prob["K"], prob["S"]).astype(np.float64)
+    M = np.linalg.inv(np.linalg.cholesky(theta))
+    psi = np.zeros_like(theta)
+    psi[1:] = M[1:] @ phi[1:] @ M[:-1].transpose(0, 2, 1)
+    return M, psi, np.einsum("bij,bj->bi", M, gam), io
+
+
+@pytest.mark.parametrize("name", ["iiwa50_s0", "iiwa50_dense", "iiwa50_mild", "iiwa33", "iiwa2"])
+def test_kernel5_first_half_vs_fp64(name):
+    prob = {"iiwa50_s0": lambda: iiwa_like(K=50, seed=0),
+            "iiwa50_dense": lambda: iiwa_like(K=50, seed=4, dense_G=True, dense_AB=True),
+            "iiwa50_mild": lambda: iiwa_like(K=50, seed=2, preset="mild", rho=1e-1),
+            "iiwa33": lambda: iiwa_like(K=33, seed=5), "iiwa2": lambda: iiwa_like(K=2, seed=6)}[name]()
+    pl = plan_of(prob)
+    d = pl.scaled_debug(prob["G_val"], prob["C_val"], prob["g"], prob["c"], prob["rho"])
+    M, psi, gh, _ = _scaled_reference(prob)
+    # theta itself carries the FP32 rounding of the Schur phase (1e-6 relative between two FP32 orders of summation);
+    # M inherits it times cond(theta)
+    assert close(d["M"], M, 2e-4), (rel2(d["M"], M), relmax(d["M"], M))
+    assert close(d["psi"], psi, 2e-4), (rel2(d["psi"], psi), relmax(d["psi"], psi))
+    assert close(d["gamma_hat"], gh, 2e-4), (rel2(d["gamma_hat"], gh), relmax(d["gamma_hat"], gh))
+    # what must hold to ~1e-7 whatever theta's last bits are: M theta M^T = I with the kernel's OWN M and theta,
+    # i.e. M^-1 M^-T reproduces the oracle's theta to FP32 rounding
+    Mi = np.linalg.inv(d["M"].astype(np.float64))
+    _, _, io = oracle(prob)
+    theta = (-io["schur"]["S_st"][:, 1]).astype(np.float64)
+    assert close(Mi @ Mi.transpose(0, 2, 1), theta, 2e-5)
+    pl.close()
+
+
+K5_CASES = {
+    "iiwa50_s0": lambda: iiwa_like(K=50, seed=0),
+    "iiwa50_s1": lambda: iiwa_like(K=50, seed=1),
+    "iiwa50_dense": lambda: iiwa_like(K=50, seed=4, dense_G=True, dense_AB=True),
+    "iiwa50_mild_rho1e-1": lambda: iiwa_like(K=50, seed=2, preset="mild", rho=1e-1),
+    "iiwa50_rho1e-4": lambda: iiwa_like(K=50, seed=3, rho=1e-4),
+    "iiwa56_max": lambda: iiwa_like(K=56, seed=2),
+    "iiwa33": lambda: iiwa_like(K=33, seed=5),
+    "iiwa9": lambda: iiwa_like(K=9, seed=1),
+    "iiwa2": lambda: iiwa_like(K=2, seed=6),
+    "iiwa1": lambda: iiwa_like(K=1, seed=6),
+}
+
+
+@pytest.mark.parametrize("name", list(K5_CASES))
+def test_kernel5_solve_vs_oracle(name):
+    prob = K5_CASES[name]()
+    pl = plan_of(prob)
+    pl.set_kernel(5)
+    assert pl.kernel() == 5
+    lam, dz, info = gpu(pl, prob)
+    lam_o, dz_o, io = oracle(prob)
+    assert close(lam, lam_o) and close(dz, dz_o), (rel2(lam, lam_o), relmax(lam, lam_o), rel2(dz, dz_o))
+    assert abs(info["iters"] - io["iters"]) <= 1, (info["iters"], io["iters"])
+    # edge cases of the loop (src/gato_pcg.cuh:300-437): max_iters = 0 and a cap below convergence
+    lam0, dz0, i0 = gpu(pl, dict(prob, max_iters=0))
+    assert i0["iters"] == 0 and not lam0.any()
+    lam7, _, i7 = gpu(pl, dict(prob, max_iters=7))
+    lam7o, _, i7o = oracle(dict(prob, max_iters=7))
+    if io["iters"] > 7:
+        assert i7["iters"] == 7 and close(lam7, lam7o, 1e-3)
+    pl.close()
+
+
+def test_kernel5_vs_reference_goldens():
+    import json
+    here = os.path.dirname(os.path.abspath(__file__))
+    n = 0
+    for path in sorted(glob.glob(os.path.join(here, "golden", "ref_iiwa50*.npz"))):
+        d = np.load(path)
+        prob = make_problem(json.loads(str(d["case"])))
+        pl = plan_of(prob)
+        pl.set_kernel(5)
+        lam, dz, info = gpu(pl, prob)
+        S = prob["S"]
+        assert close(lam, d["lam"]) and close(dz[:-S], d["dz"][:-S]), (path, rel2(lam, d["lam"]))
+        assert abs(info["iters"] - int(d["iters"])) <= 1
+        pl.close()
+        n += 1
+    assert n >= 4
+
+
+def test_kernel5_batch_matches_single_and_oracle():
+    """Per-system matrices, more systems than one pass through the scratch buffer holds (chunks of 2 x SM count) and
+    more than the resident CTAs of either kernel; an explicit small chunk gives the same bits."""
+    n = 700
+    b = iiwa_like_batch_fast(n, 14, 7, 50, seed=4242)
+    rng = np.random.default_rng(6)
+    b["G_val"] = (b["G_val"] * (1.0 + 0.2 * rng.random(b["G_val"].shape))).astype(np.float32)
+    pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
+    pl.set_kernel(5)
+    args = (b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    lam, dz, it, _ = pl.solve_batched(*args)
+    pl.set_scaled_chunk(37)
+    lam2, dz2, it2, _ = pl.solve_batched(*args)
+    assert np.array_equal(lam, lam2) and np.array_equal(dz, dz2) and np.array_equal(it, it2)
+    p1 = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"])
+    p1.set_kernel(5)
+    for i in (0, 147, 148, 295, 296, 297, 500, 592, n - 1):
+        l1, d1, i1 = gpu(p1, _sys_of(b, i))
+        assert np.array_equal(l1, lam[i]) and np.array_equal(d1, dz[i]) and i1["iters"] == it[i], i
+    for i in range(0, n, 50):
+        lam_o, dz_o, io = oracle(_sys_of(b, i))
+        assert close(lam[i], lam_o) and close(dz[i], dz_o), (i, rel2(lam[i], lam_o))
+        assert abs(int(it[i]) - io["iters"]) <= 1
+    # shared-matrix form (ld = 0) and the same results from the one-CTA kernel within the tolerance
+    pl.set_scaled_chunk(0)
+    lam3, dz3, it3, _ = pl.solve_batched(b["G_val"][0], b["C_val"][0], b["g"], b["c"], None, b["exit_tol"],
+                                         b["max_iters"], 0, b["rho"])
+    assert np.array_equal(lam3[0], lam[0])
+    pl.set_kernel(2)
+    lam4, dz4, it4, _ = pl.solve_batched(*args)
+    assert np.abs(it4.astype(int) - it.astype(int)).max() <= 1
+    assert max(rel2(lam[i], lam4[i]) for i in range(n)) < 1e-4
+    p1.close()
+    pl.close()
