@@ -166,7 +166,7 @@ def _cpu_worker(job):
     return time.perf_counter() - t0, its
 
 
-def cpu_baseline(per_core=96, cores=None):
+def cpu_baseline(per_core=96, cores=None, scipy_per_core=0):
     """Oracle port (NumPy Schur + PCG, FP32) over `cores` processes, `per_core` systems each."""
     import multiprocessing as mp
 
@@ -179,10 +179,18 @@ def cpu_baseline(per_core=96, cores=None):
     wall = time.perf_counter() - t0          # includes process start-up: report the slowest worker
     busy = max(r[0] for r in res)
     n = per_core * cores
-    return {"value": n / busy, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} IIWA-50 systems of the same generator ({per_core} per process, {cores} processes, "
-                      f"NumPy oracle Schur+PCG FP32; slowest worker {busy:.1f} s, wall {wall:.1f} s)",
-            "mean_iters": float(np.mean([i for r in res for i in r[1]]))}
+    out = {"value": n / busy, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"{n} IIWA-50 systems of the same generator ({per_core} per process, {cores} processes, "
+                     f"NumPy oracle Schur+PCG FP32; slowest worker {busy:.1f} s, wall {wall:.1f} s)",
+           "mean_iters": float(np.mean([i for r in res for i in r[1]]))}
+    if scipy_per_core > 0:   # C1 (SciPy CG on the sparse Schur complement, stair LinearOperator) and C2 (spsolve)
+        try:
+            from oracle import scipy_baseline as sb
+            out["scipy_schur_cg"] = sb.batched("schur_cg", scipy_per_core, cores, seed=SEED)
+            out["scipy_kkt_spsolve_fp64"] = sb.batched("kkt_spsolve", 4 * scipy_per_core, cores, seed=SEED)
+        except Exception as e:   # SciPy missing on the box: the NumPy port above is the baseline
+            out["scipy_error"] = repr(e)[:200]
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -194,63 +202,109 @@ import numpy as np
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[2])
 import gpu_library
 from gato_python_b200.problems import iiwa_like_batch_fast
-n, steps, warmup, seed = int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6])
-b = iiwa_like_batch_fast(n, 14, 7, 50, seed=seed, first=0)
+n, steps, warmup, seed, first = (int(x) for x in sys.argv[3:8])
+b = iiwa_like_batch_fast(n, 14, 7, 50, seed=seed, first=first)
 Gr, Gc, Cr, Cc = b["G_row"].tolist(), b["G_col"].tolist(), b["C_row"].tolist(), b["C_col"].tolist()
 lam0 = [0.0] * 700
-# the reference's API takes Python sequences: the conversion of this system's arrays to lists is
-# part of the call a user makes, so it stays inside the timed region
+tol, mit, rho = float(b["exit_tol"]), int(b["max_iters"]), float(b["rho"])
+# The reference's API takes Python sequences.  The NumPy -> list conversion of every system's arrays is done ONCE here,
+# outside the timed loop (our arm pays no conversion either); its cost is reported on its own.
+t0 = time.perf_counter()
+vals = [(b["G_val"][i].tolist(), b["C_val"][i].tolist(), b["g"][i].tolist(), b["c"][i].tolist()) for i in range(n)]
+conv_us = (time.perf_counter() - t0) / n * 1e6
 def step():
-    for i in range(n):
-        gpu_library.linsys_solve(Gr, Gc, b["G_val"][i].tolist(), Cr, Cc, b["C_val"][i].tolist(),
-                                 b["g"][i].tolist(), b["c"][i].tolist(), lam0, 1, float(b["exit_tol"]),
-                                 int(b["max_iters"]), False, float(b["rho"]))
+    for Gv, Cv, gv, cv in vals:
+        gpu_library.linsys_solve(Gr, Gc, Gv, Cr, Cc, Cv, gv, cv, lam0, 1, tol, mit, False, rho)
 for _ in range(warmup): step()
 t0 = time.perf_counter()
 for _ in range(steps): step()
 wall = time.perf_counter() - t0
 # single-solve latency as the reference itself reports it (its own cudaEvent bracket, avg of 50)
-gpu_library.linsys_solve(Gr, Gc, b["G_val"][0].tolist(), Cr, Cc, b["C_val"][0].tolist(), b["g"][0].tolist(),
-                         b["c"][0].tolist(), lam0, 50, float(b["exit_tol"]), int(b["max_iters"]), False, float(b["rho"]))
+gpu_library.linsys_solve(Gr, Gc, vals[0][0], Cr, Cc, vals[0][1], vals[0][2], vals[0][3], lam0, 50, tol, mit, False, rho)
 sys.stdout.flush()
-sys.stderr.write("GATO_REF_RESULT " + json.dumps({"wall": wall, "n": n, "steps": steps}) + "\n")
+sys.stderr.write("GATO_REF_RESULT " + json.dumps({"wall": wall, "n": n, "steps": steps, "list_conversion_us": conv_us}) + "\n")
 """
 
 
+def bench_config(args, world):
+    """The workload both arms are quoted on (identical dict in both lines)."""
+    return {"workload": f"iiwa50_batch{args.nsys}_per_gpu", "S": S, "C": C, "K": K, "systems_per_gpu": args.nsys,
+            "global_batch": args.nsys * world, "per_system_matrices": True, "exit_tol": 1e-6, "rho": 1e-3,
+            "max_iters": 500, "parallelism": f"batch-shard x{world} (no collective)"}
+
+
+def reference_kernel_only():
+    """the reference's five kernels on pre-allocated buffers through oracle/ref_harness.cu
+    (the reference's src/*.cuh included unchanged), IIWA-50 seed 0.  None when the harness did not travel."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import refharness
+        from gato_python_b200.problems import iiwa_like
+        if refharness.harness_path(S, C, K) is None:
+            return None
+        return refharness.kernel_only_summary(S, C, K, iiwa_like(S, C, K, seed=0), reps=300, warmup=20)
+    except Exception as e:
+        return {"error": repr(e)[:200]}
+
+
 def reference_arm(args, rank):
+    """The UNMODIFIED reference CUDA build through its own gpu_library.linsys_solve, looped over a bounded sample of the
+    workload: ONE PROCESS PER GPU ("multi-GPU = N independent processes"), rates summed."""
     if rank != 0:
         return
     import re
 
     ref_dir = os.path.join(ROOT, "oracle", "_ref", f"S{S}_C{C}_K{K}")
     n = args.ref_sample
+    ngpu = max(args.gpus, 1)
     base = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"iiwa50_batch{args.nsys}_per_gpu", "S": S, "C": C, "K": K,
-                       "exit_tol": 1e-6, "rho": 1e-3, "sample_per_step": n}}
+            "dtype": "f32", "data": "synthetic", "config": bench_config(args, ngpu)}
     have = os.path.isdir(ref_dir) and any(f.startswith("gpu_library") for f in os.listdir(ref_dir))
     if have:
-        r = subprocess.run([sys.executable, "-c", _REF_CHILD, ref_dir, ROOT, str(n), str(args.steps),
-                            str(args.warmup), str(SEED)], capture_output=True, text=True, timeout=1500)
-        m = re.search(r"GATO_REF_RESULT (\{.*\})", r.stderr)
-        if r.returncode == 0 and m:
-            res = json.loads(m.group(1))
-            val = res["n"] * res["steps"] / res["wall"]
-            avg = re.findall(r"avg time: ([\d.eE+-]+)", r.stdout)
-            its = re.findall(r"first run PCG terminated in (\d+) iterations", r.stdout)
-            base.update(value=val, ms_per_step=res["wall"] / res["steps"] * 1e3,
+        procs = []
+        for gi in range(ngpu):
+            env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(gi))
+            for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+                env.pop(k, None)
+            procs.append(subprocess.Popen([sys.executable, "-c", _REF_CHILD, ref_dir, ROOT, str(n), str(args.steps),
+                                           str(args.warmup), str(SEED), str(gi * args.nsys)], stdout=subprocess.PIPE,
+                                          stderr=subprocess.PIPE, text=True, env=env))
+        outs = [p.communicate(timeout=1500) + (p.returncode,) for p in procs]
+        res = []
+        for so, se, rc in outs:
+            m = re.search(r"GATO_REF_RESULT (\{.*\})", se)
+            if rc == 0 and m:
+                res.append((json.loads(m.group(1)), so))
+        if len(res) == ngpu:
+            rates = [r["n"] * r["steps"] / r["wall"] for r, _ in res]
+            val = float(sum(rates))
+            avg = re.findall(r"avg time: ([\d.eE+-]+)", res[0][1])
+            its = re.findall(r"first run PCG terminated in (\d+) iterations", res[0][1])
+            ko = reference_kernel_only()
+            per_call_us = 1e6 / rates[0]
+            single = {"ref_bracket_us_avg50": float(avg[-1]) * 1e3 if avg else None,
+                      "iters": int(its[-1]) if its else None, "python_call_us": per_call_us,
+                      "list_conversion_us": res[0][0]["list_conversion_us"]}
+            if ko and "kernel_us_median" in ko:
+                single.update(kernel_us_median=ko["kernel_us_median"], us_per_iter=ko["us_per_iter"],
+                              kernel_phase_us=ko["phase_us_median"], host_api_us_median=ko["host_api_us_median"],
+                              host_overhead_fraction_of_call=1.0 - ko["kernel_us_median"] / per_call_us)
+            base.update(value=val, ms_per_step=max(r["wall"] for r, _ in res) / args.steps * 1e3,
                         e2e={"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                        cpu_baseline={"value": val, "unit": UNIT, "cores": 1, "kind": "reference",
-                                      "sample": f"{n} IIWA-50 systems per step through the unmodified reference CUDA "
-                                                "build's gpu_library.linsys_solve (one host thread drives one GPU; "
-                                                "the reference ships no CPU path and no batched entry point)"},
-                        single_solve={"ref_bracket_us_avg50": float(avg[-1]) * 1e3 if avg else None,
-                                      "iters": int(its[-1]) if its else None},
-                        note="reference = its own CUDA build on GPU 0 (oracle/_ref), called in a loop")
+                        cpu_baseline={"value": val, "unit": UNIT, "cores": ngpu, "kind": "reference",
+                                      "sample": f"{n} IIWA-50 systems per step and GPU through the unmodified reference "
+                                                f"CUDA build's gpu_library.linsys_solve, {ngpu} process(es), one per "
+                                                "GPU, one host thread each (the reference ships no CPU path and no "
+                                                "batched entry point); list conversion outside the timed loop"},
+                        per_gpu_values=rates, single_solve=single,
+                        note="reference = its own CUDA build (oracle/_ref), one process per GPU, called in a loop; "
+                             "single_solve.kernel_us_median = its five kernels on pre-allocated buffers "
+                             "(oracle/ref_harness.cu): the rest of a call is host overhead (per-solve cudaMalloc / "
+                             "cudaFree / cudaDeviceSynchronize / printf, gpu_library.cu:36-81)")
             print(json.dumps(base), flush=True)
             return
-        base["reference_cuda_build_error"] = (r.stderr or r.stdout)[-300:]
+        base["reference_cuda_build_error"] = (outs[0][1] or outs[0][0])[-300:]
     # fall back: the NumPy oracle port on the host cores
     cb = cpu_baseline(per_core=max(n // max(os.cpu_count() or 1, 1), 8))
     base.update(value=cb["value"], ms_per_step=None, cpu_baseline=cb,

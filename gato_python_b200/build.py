@@ -47,6 +47,17 @@ def _lib_sources():
 BUILTIN_SIZES = [(2, 1), (4, 2), (7, 3), (14, 7)]
 
 
+def build_dev(defines=(), out=None, verbose=False):
+    """Development build: (14, 7) kernels only, extra -D defines; load it with GATO_B200_LIB=<path>."""
+    target = out or os.path.join(ROOT, "build", "dev", "libgato_b200.so")
+    os.makedirs(os.path.dirname(target), exist_ok=True)
+    cmd = [_nvcc()] + ARCH + COMMON + ["-DGATO_ONLY_IIWA"] + [f"-D{d}" for d in defines]
+    if verbose:
+        cmd += ["-Xptxas", "-v"]
+    subprocess.run(cmd + [os.path.join(CSRC, "gato_capi.cu"), "-o", target], check=True)
+    return target
+
+
 def build_library(force=False, extra_sc=None, verbose=False, out=None):
     """Compile libgato_b200.so (or, with `out`, a second copy elsewhere -- e.g. one that carries an extra
     (STATE_SIZE, CONTROL_SIZE) pair in every kernel family); returns its path."""
@@ -116,7 +127,9 @@ def build_all(force=False):
 
 
 if __name__ == "__main__":
-    if len(sys.argv) >= 5 and sys.argv[1] == "--module":
+    if len(sys.argv) >= 2 and sys.argv[1] == "--dev":
+        print(build_dev(defines=[a for a in sys.argv[2:] if "=" in a or a.isidentifier()]))
+    elif len(sys.argv) >= 5 and sys.argv[1] == "--module":
         print(build_module(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), force=True))
     else:
         for d in build_all(force="--force" in sys.argv):

@@ -544,7 +544,9 @@ void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::
 }
 
 // -DGATO_EXTRA_S/-DGATO_EXTRA_C add one more (STATE_SIZE, CONTROL_SIZE) pair to every kernel family
-#if GATO_EXTRA_S > 0
+#if defined(GATO_ONLY_IIWA)   // development builds: the (14, 7) kernels only (a fifth of the compile time)
+#define GATO_FOR_SIZES(X) X(14, 7)
+#elif GATO_EXTRA_S > 0
 #define GATO_FOR_SIZES(X) X(2, 1) X(4, 2) X(7, 3) X(14, 7) X(GATO_EXTRA_S, GATO_EXTRA_C)
 #else
 #define GATO_FOR_SIZES(X) X(2, 1) X(4, 2) X(7, 3) X(14, 7)

@@ -20,10 +20,14 @@
 #pragma once
 #include "gato_kernel_v2.cuh"
 
+#ifndef GATO_V5_CTAS
+#define GATO_V5_CTAS 2
+#endif
+
 namespace gato {
 
 template <int S, int C, int NT>
-__global__ void __launch_bounds__(NT, 2) gato_pcg_scaled(const SolveParams2 q) {
+__global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveParams2 q) {
     using L = Layout2<S, C>;
     using SL = ScaledLayout<S, C>;
     using MC = MapControl<S, C>;

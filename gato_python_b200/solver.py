@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgato_b200.so")
+# GATO_B200_LIB: another build of the same library (development builds, build.py --dev)
+LIB_PATH = os.environ.get("GATO_B200_LIB") or os.path.join(_HERE, "libgato_b200.so")
 
 WARM_OFF, WARM_REFERENCE, WARM_TRUE, WARM_RESIDENT = 0, 1, 2, 3
 PRECOND_STAIR, PRECOND_BLOCK_JACOBI = 0, 1
