@@ -398,6 +398,36 @@ def mpc_sequence(Plan, dev_index, nsteps=1000):
     return out
 
 
+def parity_sample(b, lam, dz, its, lam2, dz2, its2, n, rank):
+    """Oracle check of the timed outputs: `n` systems spread evenly over the batch (first, last, and a seeded choice in
+    between).  -> max relative errors (max of 2-norm and max-norm relative) and max iteration-count difference, for the
+    device-resident run (lam, dz, its) and the host-buffer run (lam2, dz2, its2)."""
+    from oracle import gato_oracle as orc
+
+    nsys = lam.shape[0]
+    rng = np.random.default_rng(12345 + rank)
+    n = max(min(n, nsys), 1)
+    idx = np.unique(np.concatenate([[0, nsys - 1], (np.arange(n) * nsys // n + rng.integers(0, max(nsys // n, 1), n)) % nsys]))[:max(n, 2)]
+    lam0 = np.zeros(S * K, np.float32)
+
+    def rel(a, ref):
+        ref = ref.astype(np.float64); d = a.astype(np.float64) - ref
+        return max(np.linalg.norm(d) / max(np.linalg.norm(ref), 1e-300), np.abs(d).max() / max(np.abs(ref).max(), 1e-300))
+    out = dict(n=len(idx), systems=[int(i) for i in idx[:8]] + ["..."], max_rel_lambda=0.0, max_rel_dz=0.0, max_iter_diff=0,
+               max_rel_lambda_e2e=0.0, max_rel_dz_e2e=0.0, max_iter_diff_e2e=0)
+    for i in idx:
+        lo, do, info = orc.linsys_solve_info(S, C, K, b["G_row"], b["G_col"], b["G_val"][i], b["C_row"], b["C_col"],
+                                             b["C_val"][i], b["g"][i], b["c"][i], lam0, 1, b["exit_tol"], b["max_iters"],
+                                             False, b["rho"])
+        out["max_rel_lambda"] = max(out["max_rel_lambda"], rel(lam[i], lo))
+        out["max_rel_dz"] = max(out["max_rel_dz"], rel(dz[i], do))
+        out["max_iter_diff"] = max(out["max_iter_diff"], abs(int(its[i]) - info["iters"]))
+        out["max_rel_lambda_e2e"] = max(out["max_rel_lambda_e2e"], rel(lam2[i], lo))
+        out["max_rel_dz_e2e"] = max(out["max_rel_dz_e2e"], rel(dz2[i], do))
+        out["max_iter_diff_e2e"] = max(out["max_iter_diff_e2e"], abs(int(its2[i]) - info["iters"]))
+    return out
+
+
 def ours_arm(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -413,9 +443,10 @@ def ours_arm(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=dev)
 
     # CPU baseline first (rank 0, N == 1 only), before the GPU is busy
-    cpu = None
+    cpu = refk = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline(per_core=args.cpu_per_core)
+        cpu = cpu_baseline(per_core=args.cpu_per_core, scipy_per_core=args.scipy_per_core)
+        refk = reference_kernel_only()
 
     # host placement: run and pin memory on the GPU's own NUMA node (after the CPU baseline used every core)
     numa = None
@@ -427,6 +458,11 @@ def ours_arm(args, rank, local_rank, world):
     b = iiwa_like_batch_fast(nsys, S, C, K, seed=SEED, first=rank * nsys)
     nnzG, nnzC = b["G_val"].shape[1], b["C_val"].shape[1]
     pl = Plan(S, C, K, b["G_row"], b["G_col"], b["C_row"], b["C_col"], device=local_rank, max_batch=nsys)
+    if args.kernel:
+        pl.set_kernel(args.kernel)
+    kernel_id = pl.kernel_for(nsys)
+    if kernel_id == 5:
+        pl.set_profiling(True)      # CUDA events around each half of kernel 5, on the launching stream
     n_l, n_z = pl.n_l, pl.n_z
 
     # pinned host copies (the e2e path reads these) and device-resident copies (the `value` path)
@@ -458,13 +494,20 @@ def ours_arm(args, rank, local_rank, world):
     sampler.start()
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     evs[0].record(stream)
+    halves, launches = [], 0
     for i in range(args.steps):
         step()
         evs[i + 1].record(stream)
+        if kernel_id == 5 and i >= args.steps - 3:      # last steps only: reading the events waits for the step
+            a, b2, nl = pl.last_profile()
+            halves.append((a, b2))
+            launches = nl
     barrier()
     total_ms = evs[0].elapsed_time(evs[-1])
     kern_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     iters_host = its.cpu().numpy()
+    lam_host, dz_host = lam.cpu().numpy(), dz.cpu().numpy()      # the TIMED outputs (last step), checked below
+    pl.set_profiling(False)
 
     # ---- end to end: host buffers through gato_solve_batched (H2D + kernel + D2H every step) ----
     hv = {k: v.numpy() for k, v in host.items()}
@@ -484,6 +527,26 @@ def ours_arm(args, rank, local_rank, world):
     e2e_wall = time.perf_counter() - t0
     clocks = sampler.stop()
     e2e_iters = h_it.numpy().copy()   # before the shared-matrix variant below reuses the output buffers
+    e2e_lam, e2e_dz = h_lam.numpy().copy(), h_dz.numpy().copy()
+
+    # ---- what the host <-> device links of this box carry at the same time on all ranks: a plain pinned-memory copy of
+    # the same bytes both ways (the ceiling of any host-buffer pipeline; shows whether e2e is bound by the host)
+    probe_bytes_up = sum(v.numel() * 4 for v in host.values())
+    probe_bytes_dn = (h_lam.numel() + h_dz.numel() + h_it.numel()) * 4
+    s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+    def copy_probe():
+        with torch.cuda.stream(s_up):
+            for k2, v in host.items():
+                d[k2].copy_(v, non_blocking=True)
+        with torch.cuda.stream(s_dn):
+            h_lam.copy_(lam, non_blocking=True); h_dz.copy_(dz, non_blocking=True); h_it.copy_(its, non_blocking=True)
+    copy_probe()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(max(args.steps // 2, 3)):
+        copy_probe()
+    barrier()
+    probe_wall = (time.perf_counter() - t0) / max(args.steps // 2, 3)
 
     # ---- the other reading of config 4 ("randomised g/c"): ONE matrix pair shared by all systems, only g and
     # c differ -- every system is still unpacked, factored and solved on its own; only the PCIe bytes shrink
@@ -500,13 +563,20 @@ def ours_arm(args, rank, local_rank, world):
     shared_wall = time.perf_counter() - t0
     shared_iters = float(h_it.numpy().mean())
 
-    t = torch.tensor([total_ms, e2e_wall * 1e3, e2e_dev_ms, shared_wall * 1e3], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, e2e_wall * 1e3, e2e_dev_ms, shared_wall * 1e3, probe_wall * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_wall_ms, e2e_dev_ms, shared_wall_ms = (float(x) for x in t.tolist())
+    total_ms, e2e_wall_ms, e2e_dev_ms, shared_wall_ms, probe_wall_ms = (float(x) for x in t.tolist())
 
-    # parity spot check of the timed outputs: e2e results == device-resident results (same kernel)
-    same = bool(np.array_equal(e2e_iters, iters_host))
+    # parity of the TIMED outputs against the oracle: a seeded sample of systems spread over this rank's batch, from
+    # the buffers the timed device-resident run and the timed host-buffer run left behind
+    parity = parity_sample(b, lam_host, dz_host, iters_host, e2e_lam, e2e_dz, e2e_iters, args.parity_sample, rank)
+    pt = torch.tensor([parity["max_rel_lambda"], parity["max_rel_dz"], float(parity["max_iter_diff"]),
+                       parity["max_rel_lambda_e2e"], parity["max_rel_dz_e2e"], float(parity["max_iter_diff_e2e"])],
+                      dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(pt, op=dist.ReduceOp.MAX)
+    pmax = [float(x) for x in pt.tolist()]
 
     if rank == 0:
         ms_per_step = total_ms / args.steps
@@ -519,41 +589,74 @@ def ours_arm(args, rank, local_rank, world):
         tfl = fl / (kavg_ms * 1e-3) / 1e12
         h2d = 4 * nsys * (nnzG + nnzC + n_z + n_l)
         d2h = 4 * nsys * (n_l + n_z + 1)
-        kname = "gato_fused_solve_v2" if pl.kernel() == 2 else "gato_fused_solve"
+        cfg = bench_config(args, world)
+        stats = {"nnzG": nnzG, "nnzC": nnzC, "mean_pcg_iters": float(iters_host.mean()),
+                 "max_pcg_iters": int(iters_host.max()), "kernel": kernel_id,
+                 "cache": f"inputs {bps * nsys / 1e6:.0f} MB per launch > 126 MB L2 (no flush needed)"}
+        if kernel_id == 5 and halves:
+            # the dominant kernel of kernel 5 is its second half (PCG + dz); its duration comes from CUDA events recorded
+            # around it on the launching stream (gato_plan_set_profiling), summed over the chunks of a step
+            h1 = float(np.mean([h[0] for h in halves])); h2 = float(np.mean([h[1] for h in halves]))
+            kname, kdur_ms = "gato_pcg_scaled", h2
+            launches_per_step = launches
+            halves_ms = {"gato_fused_solve_v2<SCALED> (unpack + Schur + FP64 congruence)": h1,
+                         "gato_pcg_scaled (PCG on the scaled system + dz)": h2, "share_of_step": h2 / (h1 + h2)}
+            scratch = 4 * nsys * K * 1088          # floats the first half writes and the second reads (ScaledLayout)
+        else:
+            kname = "gato_fused_solve_v2" if kernel_id == 2 else "gato_fused_solve"
+            kdur_ms, launches_per_step, halves_ms, scratch = kavg_ms, 1, None, 0
+        ach_k = bps * nsys / (kdur_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"iiwa50_batch{nsys}_per_gpu", "S": S, "C": C, "K": K, "systems_per_gpu": nsys,
-                       "global_batch": nsys * world, "per_system_matrices": True, "nnzG": nnzG, "nnzC": nnzC,
-                       "exit_tol": b["exit_tol"], "rho": b["rho"], "max_iters": b["max_iters"],
-                       "mean_pcg_iters": float(iters_host.mean()), "max_pcg_iters": int(iters_host.max()),
-                       "cluster_ctas_x_knots": list(pl.cluster()), "parallelism": f"batch-shard x{world} (no collective)",
-                       "cache": f"inputs {bps * nsys / 1e6:.0f} MB per launch > 126 MB L2 (no flush needed)"},
+            "config": cfg, "stats": stats,
             "e2e": {"value": nsys * world * args.steps / (e2e_wall_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "timing": "wall clock, max over ranks",
                     "device_event_value": nsys * world * args.steps / (e2e_dev_ms * 1e-3),
-                    "outputs_match_resident_run": same, "host_numa_binding": numa},
+                    "host_numa_binding": numa,
+                    "bytes_per_system": (h2d + d2h) / nsys,
+                    "aggregate_gbs": (h2d + d2h) * world * args.steps / (e2e_wall_ms * 1e-3) / 1e9,
+                    "pinned_copy_probe": {"aggregate_gbs": (probe_bytes_up + probe_bytes_dn) * world / (probe_wall_ms * 1e-3) / 1e9,
+                                          "solves_per_s_ceiling": nsys * world / (probe_wall_ms * 1e-3),
+                                          "what": "the same H2D and D2H bytes as one e2e step, plain cudaMemcpyAsync from / "
+                                                  "to pinned memory on two streams, all ranks at once, max over ranks: "
+                                                  "no host-buffer pipeline on this box can beat it"}},
             "e2e_shared_matrix": {"value": nsys * world * args.steps / (shared_wall_ms * 1e-3), "unit": UNIT,
                                   "h2d_bytes_per_step": 4 * (nnzG + nnzC + nsys * (n_z + n_l)),
                                   "d2h_bytes_per_step": d2h, "mean_pcg_iters": shared_iters,
                                   "note": "same call, G_val/C_val of system 0 shared by all systems (ld = 0), g and c "
                                           "per system; every system is still factored and solved independently"},
-            "gpu_launches": args.steps,
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "parity_sample": {"n": parity["n"] * world, "systems": parity["systems"], "checker": "NumPy oracle (oracle/gato_oracle.py)",
+                              "max_rel_lambda": pmax[0], "max_rel_dz": pmax[1], "max_iter_diff": int(pmax[2]),
+                              "e2e": {"max_rel_lambda": pmax[3], "max_rel_dz": pmax[4], "max_iter_diff": int(pmax[5])},
+                              "bar": "2-norm and max-norm relative <= 1e-4, iterations +-1", 
+                              "pass": bool(max(pmax[0], pmax[1], pmax[3], pmax[4]) <= 1e-4 and max(pmax[2], pmax[5]) <= 1)},
+            "gpu_launches": args.steps * launches_per_step,
+            "roofline": {"bound": "hbm", "achieved": ach_k, "peak": peak, "unit": "GB/s", "frac": ach_k / peak,
                          "traffic": ncu_traffic(kname, nsys), "peak_source": peak_src,
                          "kernel": kname, "algorithmic_bytes_per_launch": bps * nsys,
-                         "kernel_ms_avg": kavg_ms, "algorithmic_bytes_per_system": bps,
+                         "kernel_ms_avg": kdur_ms, "algorithmic_bytes_per_system": bps,
+                         "launches_per_step": launches_per_step, "kernel_5_halves_ms_per_step": halves_ms,
+                         "scratch_bytes_per_step_written_then_read": scratch,
+                         "whole_step": {"achieved": ach, "frac": ach / peak, "ms": kavg_ms},
                          "fp32": {"achieved_tflops": tfl, "peak_tflops": FP32_PEAK_TFLOPS,
                                   "frac": tfl / FP32_PEAK_TFLOPS, "flops_per_launch": fl,
                                   "peak_source": "theoretical 148 SM x 128 lanes x 2 x 1.965 GHz",
-                                  "note": "arithmetic intensity ~100 flop/B >> 11.5 flop/B machine balance: "
-                                          "the kernel is FP32-pipe/latency bound; the HBM fraction is a sanity ceiling"}},
+                                  "note": "whole step (all launches), SURVEY 8(d) algorithmic flop count of the "
+                                          "reference's formulation; arithmetic intensity ~100 flop/B >> 11.5 flop/B "
+                                          "machine balance: FP32-pipe/latency bound, the HBM fraction is a sanity ceiling"}},
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
+        if refk is not None:
+            line["reference_kernel_only"] = refk
         if world == 1 and not args.no_single:
             line["single_solve"] = single_solve_latency(torch, Plan, local_rank)
+            if refk and "kernel_us_median" in refk:
+                line["single_solve"]["reference_kernel_only_us"] = refk["kernel_us_median"]
+                line["single_solve"]["speedup_vs_reference_kernels"] = refk["kernel_us_median"] / line["single_solve"]["kernel_us_median"]
+                line["single_solve"]["reference_us_per_iter"] = refk["us_per_iter"]
             line["single_solve_k256"] = single_solve_latency(torch, Plan, local_rank, reps=100, knots=256)
             line["mpc_sequence"] = mpc_sequence(Plan, local_rank)
         print(json.dumps(line), flush=True)
@@ -561,6 +664,44 @@ def ours_arm(args, rank, local_rank, world):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def single_process_multi_gpu(args):
+    """`--single-process-gpus N`: ONE process drives N GPUs through gato_solve_batched_multi (one host thread per device,
+    contiguous slices of ONE pinned host buffer each way).  The timed region is H2D + solve + the D2H
+    gather; prints one JSON line.  Not the driver's contract (that is torchrun, one process per GPU): an extra view."""
+    import torch
+
+    from gato_python_b200 import MultiPlan
+    from gato_python_b200.problems import iiwa_like_batch_fast
+
+    n_gpu = args.single_process_gpus
+    nsys = args.nsys * n_gpu
+    b = iiwa_like_batch_fast(nsys, S, C, K, seed=SEED, first=0)
+    mp = MultiPlan(S, C, K, b["G_row"], b["G_col"], b["C_row"], b["C_col"], devices=list(range(n_gpu)), max_batch=args.nsys)
+    host = {k: torch.from_numpy(b[k]).pin_memory().numpy() for k in ("G_val", "C_val", "g", "c")}
+    out = (torch.empty((nsys, mp.n_l)).pin_memory().numpy(), torch.empty((nsys, mp.n_z)).pin_memory().numpy(),
+           torch.empty(nsys, dtype=torch.int32).pin_memory().numpy())
+
+    def step():
+        return mp.solve_batched(host["G_val"], host["C_val"], host["g"], host["c"], None, b["exit_tol"], b["max_iters"],
+                                0, b["rho"], out=out)[3]
+    for _ in range(max(args.warmup, 3)):
+        step()
+    t0 = time.perf_counter()
+    dev_ms = [step() for _ in range(args.steps)]
+    wall = time.perf_counter() - t0
+    par = parity_sample(b, out[0], out[1], out[2], out[0], out[1], out[2], args.parity_sample, 0)
+    nnzG, nnzC = b["G_val"].shape[1], b["C_val"].shape[1]
+    h2d = 4 * nsys * (nnzG + nnzC + mp.n_z + mp.n_l)
+    d2h = 4 * nsys * (mp.n_l + mp.n_z + 1)
+    print(json.dumps({"metric": METRIC, "mode": "single process, one host thread per GPU (gato_solve_batched_multi)",
+                      "n_gpus": n_gpu, "value": nsys * args.steps / wall, "unit": UNIT, "steps": args.steps,
+                      "ms_per_step": wall / args.steps * 1e3, "longest_device_ms_per_step": float(np.mean(dev_ms)),
+                      "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                      "aggregate_gbs": (h2d + d2h) * args.steps / wall / 1e9, "config": bench_config(args, n_gpu),
+                      "parity_sample": {k: par[k] for k in ("n", "max_rel_lambda", "max_rel_dz", "max_iter_diff")}}), flush=True)
+    mp.close()
 
 
 def main():
@@ -572,6 +713,11 @@ def main():
     ap.add_argument("--nsys", type=int, default=8192, help="systems per GPU per step")
     ap.add_argument("--ref-sample", type=int, default=64, help="systems per step for --impl reference")
     ap.add_argument("--cpu-per-core", type=int, default=1024, help="systems per process for cpu_baseline")
+    ap.add_argument("--scipy-per-core", type=int, default=8, help="systems per process for the SciPy baselines (0 = skip)")
+    ap.add_argument("--parity-sample", type=int, default=64, help="systems per rank checked against the oracle")
+    ap.add_argument("--kernel", type=int, default=0, help="force a kernel (0 = automatic selection)")
+    ap.add_argument("--single-process-gpus", type=int, default=0,
+                    help="extra mode: one process drives N GPUs through gato_solve_batched_multi (host buffers)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-single", action="store_true")
     args = ap.parse_args()
@@ -580,6 +726,10 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         reference_arm(args, rank)
+        return
+    if args.single_process_gpus > 0:
+        if rank == 0:
+            single_process_multi_gpu(args)
         return
     ours_arm(args, rank, local_rank, world)
 

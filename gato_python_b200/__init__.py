@@ -4,5 +4,5 @@ Product code: `csrc/` (CUDA kernels + C ABI, include/gato_b200.h), `solver.py` (
 the host-side mirror of `gpu_library.linsys_solve`), `build.py` (in-tree nvcc build),
 `problems.py` (synthetic KKT systems), `sharding.py` (batch sharding over GPUs).
 """
-from .solver import (GatoError, Plan, PRECOND_BLOCK_JACOBI, PRECOND_STAIR, WARM_OFF, WARM_REFERENCE,  # noqa: F401
+from .solver import (GatoError, MultiPlan, Plan, PRECOND_BLOCK_JACOBI, PRECOND_STAIR, WARM_OFF, WARM_REFERENCE,  # noqa: F401
                      WARM_TRUE, device_count, linsys_solve, supported_sizes)

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/gato_b200.h"
@@ -111,6 +112,11 @@ struct gato_plan {
     cudaStream_t scr_stream[kScr] = {};
     int nscr = 0;
     int v5_chunk = 0;       // kernel 5: systems per chunk (0 = automatic)
+    int profile = 0;        // kernel 5: record CUDA events around each of its launches (gato_plan_set_profiling)
+    std::vector<cudaEvent_t> prof_ev;   // 3 per chunk of the last profiled call: before first half | between | after second
+    int prof_chunks = 0, prof_launches = 0;
+    int batch_hint = 0;     // > 0 inside gato_solve_batched: the size of the whole call, so that every chunk of its
+                            // pipeline runs the kernel the whole batch selects
     PinBuf hin, hout;   // pinned staging for the single-solve path
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -277,13 +283,13 @@ int launch_v2_sc(const gato_plan* pl, const gato::SolveParams2& q, cudaStream_t 
 // half = PCG on S^ = I + O^ + dz (2 CTAs per SM); they meet in a per-plan scratch buffer that holds one chunk of
 // systems (ScaledLayout::KSCR floats per knot) and is reused chunk after chunk, so it stays in the 126 MB L2.
 template <int S> struct HasV5 { static constexpr bool value = (S == 14); };
-constexpr int kV5Threads = 224;
+constexpr int kV5Threads = 128;     // second half: two lanes per knot, up to 64 knots
 
 template <int S, int C>
 int v5_ok_sc(const gato_plan* pl) {
     if constexpr (HasV5<S>::value) {
         using L = gato::Layout2<S, C>;
-        return (L::LPK * pl->K <= kV5Threads && v2_pick_nt<S, C>(pl) > 0) ? 1 : 0;
+        return (2 * pl->K <= kV5Threads && v2_pick_nt<S, C>(pl) > 0) ? 1 : 0;
     } else {
         return 0;
     }
@@ -327,8 +333,8 @@ template <int S, int C>
 int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
     if constexpr (HasV5<S>::value) {
         using L = gato::Layout2<S, C>;
-        constexpr int NT = kV5Threads, NKP = (NT / 32) * L::KPW;
-        constexpr size_t smem = (size_t)(4 * (NKP + 2) * L::VS + NKP * (L::VS + L::LDC) + 64) * sizeof(float);
+        constexpr int NT = kV5Threads, NKP = NT / 2;
+        constexpr size_t smem = (size_t)(4 * (2 * (NKP + 2) * L::HALFP + 4) + NKP * (L::VS + L::LDC) + 64) * sizeof(float);
         auto kern = gato::gato_pcg_scaled<S, C, NT>;
         if (pl->occp_val == 0) {
             int occ = 0;
@@ -354,7 +360,7 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
         return fail(GATO_EUNSUPPORTED, "kernel 5 has no true warm start yet (use kernel 2 for GATO_WARM_TRUE)");
     const long long per = v5_scratch_per_system<S, C>(pl);
     const int sms = pl->sm_count > 0 ? pl->sm_count : 148;
-    int chunk = pl->v5_chunk > 0 ? pl->v5_chunk : 2 * sms;
+    int chunk = pl->v5_chunk > 0 ? pl->v5_chunk : 16 * sms;   // measured: larger chunks win although the scratch then leaves L2
     if (chunk > q.p.nsys) chunk = q.p.nsys;
     int si = 0;
     while (si < pl->nscr && pl->scr_stream[si] != st) ++si;
@@ -367,13 +373,27 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
     q.scr = (float*)pl->dscr[si].p;
     q.scr_ld = per;
     const gato::SolveParams base = q.p;
-    for (int r0 = 0; r0 < base.nsys; r0 += chunk) {
+    const int nchunk = (base.nsys + chunk - 1) / chunk;
+    const bool prof = pl->profile && !first_only;
+    if (prof) {
+        while ((int)pl->prof_ev.size() < 3 * nchunk) {
+            cudaEvent_t e;
+            GATO_CUDA(cudaEventCreate(&e));
+            pl->prof_ev.push_back(e);
+        }
+        pl->prof_chunks = 0;
+    }
+    for (int r0 = 0, ci = 0; r0 < base.nsys; r0 += chunk, ++ci) {
         const int nr = base.nsys - r0 < chunk ? base.nsys - r0 : chunk;
         q.p = slice_params(base, r0, nr);
+        if (prof) GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci], st));
         int rc = launch_v5_first<S, C>(pl, q, st);
         if (rc || first_only) return rc;
+        if (prof) GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci + 1], st));
         if ((rc = launch_v5_second<S, C>(pl, q, st))) return rc;
+        if (prof) { GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci + 2], st)); pl->prof_chunks = ci + 1; }
     }
+    pl->prof_launches = 2 * nchunk;
     return GATO_OK;
 }
 
@@ -619,6 +639,17 @@ bool v5_ok(const gato_plan* pl) {
 
 bool use_v5(const gato_plan* pl) { return pl->kernel == 5 && v5_ok(pl); }
 
+// automatic choice for a call of `nsys` systems: kernel 5 for batches that fill the device (its two kernels keep two to
+// three systems per SM in flight: measured 2.3 M vs 2.0 M solves/s at 8192 IIWA-50 systems), the one-CTA kernel for
+// single solves and small batches (one launch; the zero-copy single solve needs its TMA staging) and for true warm
+// starts, which kernel 5 does not implement
+bool use_v5_for(const gato_plan* pl, int nsys, int warm) {
+    if (pl->kernel == 5) return v5_ok(pl);
+    if (pl->kernel != 0 || pl->cl_override > 0 || warm == 2) return false;
+    if (pl->batch_hint > 0) nsys = pl->batch_hint;
+    return nsys >= (pl->sm_count > 0 ? pl->sm_count : 148) && v5_ok(pl);
+}
+
 long long v5_scratch_floats(const gato_plan* pl) {
 #define X(s, c) if (pl->S == s && pl->C == c) return v5_scratch_per_system<s, c>(pl);
     GATO_FOR_SIZES(X)
@@ -738,7 +769,7 @@ int launch_solve_v2grid(gato_plan* pl, const gato::SolveParams& p, cudaStream_t 
 
 // the kernel the plan selects; dumps of the Schur intermediates exist only in the cluster kernel
 int launch_auto(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
-    if (p.dbg_S == nullptr && use_v5(pl)) return launch_solve_v5(pl, p, st);
+    if (p.dbg_S == nullptr && use_v5_for(pl, p.nsys, p.warm)) return launch_solve_v5(pl, p, st);
     if (p.dbg_S == nullptr && use_v2(pl)) return launch_solve_v2(pl, p, st);
     if (p.dbg_S == nullptr && use_v2cl(pl)) return launch_solve_v2cl(pl, p, st);
     if (p.dbg_S == nullptr && use_v2grid(pl)) return launch_solve_v2grid(pl, p, st);

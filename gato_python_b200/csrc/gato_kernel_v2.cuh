@@ -92,17 +92,18 @@ struct Layout2 {
 
 // Kernel 5: what its first half (Schur + congruence, FP64) hands to its second half (PCG + dz) through global memory,
 // per knot, in floats.  [0, REG): verbatim copy of the knot's shared-memory region A | B | Q^-1 | R^-1 | q | r (the dz
-// phase reads it with the same offsets); PSI: psi_b = M_b phi_b M_{b-1}^T in lane-ready order (LPK lanes x PSIL floats:
-// lane (g, h) holds rows g*R + rp_h(i) x columns h*HALFU + cp_g(j), rp / cp = the half-swap permutation when the flag
-// is set, so that both reduce-scatters of the PCG loop are select-free); M: M_b row-major [S][VS] in pos layout (the
-// final lambda = M^T lambda^); GAM: gamma^_b in pos layout.
+// phase reads it with the same offsets; with a diagonal cost pattern only the diagonal of Q^-1 is copied); PSI:
+// psi_b = M_b phi_b M_{b-1}^T in lane-ready order of the second half (2 lanes x PSIL floats: lane g holds rows g S/2 ..
+// as two row-major S/2 x S/2 blocks, the column half g first); M: M_b row-major [S][VS] in pos layout (the final
+// lambda = M^T lambda^); GAM: gamma^_b in pos layout.
 template <int S, int C>
 struct ScaledLayout {
     using L = Layout2<S, C>;
     static constexpr int REG = L::oPhi;
-    static constexpr int PSIL = (L::R * L::HALFU + 3) & ~3;
+    static constexpr int PSIB = (L::R * L::HALFU + 3) & ~3;   // one R x HALFU block, row-major, padded to 16 bytes
+    static constexpr int PSIL = 2 * PSIB;                     // lane g of the second half: [block of its column half g | other half]
     static constexpr int oPSI = REG;
-    static constexpr int oM = oPSI + L::LPK * PSIL;
+    static constexpr int oM = oPSI + 2 * PSIL;
     static constexpr int oGAM = oM + S * L::VS;
     static constexpr int KSCR = oGAM + L::VS;
     // FP64 scratch inside a knot's (dead) shared-memory region: M64 [S][S] doubles, then T64 [S][2 HT] doubles
@@ -111,11 +112,6 @@ struct ScaledLayout {
     static_assert(L::H == 2 && L::LPK == 4, "kernel 5 is written for the 2 x 2 lane split (even S > 8)");
     static_assert(oT64 + 2 * S * 2 * HT <= L::KN0, "FP64 scratch must fit the knot region");
     static_assert(REG % 4 == 0 && KSCR % 4 == 0, "16-byte aligned sections");
-    // the half-swap permutation of R rows (or HALFU columns): [OWN .. R) first, so that the rows a lane keeps and the
-    // rows it sends in a reduce-scatter sit in the same registers for both lanes of a pair
-    __host__ __device__ static constexpr int hswap(int i) {
-        return (i + L::OWN < L::R) ? i + L::OWN : (i >= L::OWN ? i - L::OWN : i);
-    }
 };
 
 // row maps for the in-register Gauss-Jordan: which lane-in-knot / register holds row r

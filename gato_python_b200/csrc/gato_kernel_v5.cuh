@@ -1,14 +1,17 @@
 // gato_kernel_v5.cuh -- SECOND HALF OF KERNEL 5: PCG on the scaled system S^ = I + O^ and the dz recovery, sm_100a.
 //
 // The first half (gato_fused_solve_v2<.., SCALED = true>, gato_kernel_v5_schur.inc) leaves per knot, in global scratch
-// (ScaledLayout): psi_b = M_b phi_b M_{b-1}^T in lane-ready order, gamma^_b, M_b and a copy of the knot region.
-// This kernel keeps ONE S/2 x S/2 block of psi_b per lane in registers (49 words for S = 14, against 196 matrix words
-// per lane in the one-CTA kernel) and uses every word twice per product,
-//     u_b     += psi_b   x_{b-1}      (rows of this knot)
-//     w_{b-1} += psi_b^T x_b          (rows of the LEFT knot: O^ is symmetric, S^[b-1, b] = psi_b^T)
-// so a 224-thread CTA needs < 128 registers per thread and ~14 KB of shared memory: TWO systems are resident per SM
-// and one system's reduction chains and barriers hide behind the other's arithmetic.  Per iteration and lane:
-// 4 x 49 FFMA + 16 shuffles + 4 block barriers, against 7 x 49 FFMA + 16 shuffles + 4 barriers before.
+// (ScaledLayout): psi_b = M_b phi_b M_{b-1}^T, gamma^_b, M_b and a copy of the knot region.
+//
+// Mapping: TWO lanes per knot.  Lane (b, g) keeps rows g S/2 .. of psi_b -- 7 x 14 = 98 words for S = 14, against
+// 196 matrix words per lane and four lanes per knot in the one-CTA kernel -- and uses every word twice per product,
+//     u_b     += psi_b   x_{b-1}      (its rows of this knot: complete in the lane, no combine)
+//     w_{b-1} += psi_b^T x_b          (partial over its rows; the LEFT knot's rows: O^ is symmetric, S^[b-1, b] = psi_b^T)
+// so an IIWA-50 system is four warps, a CTA needs < 170 registers per thread and ~15 KB of shared memory, and THREE
+// systems are resident per SM (one warp of each per sub-partition): one system's reduction chains and barriers hide
+// behind the others' arithmetic.  Per iteration and lane: 4 x 98 FFMA against 8 + 4 128-bit shared-memory loads and
+// 14 + 10 shuffles -- the first version of this kernel (four lanes per knot, 7 x 7 blocks) issued twice the shared
+// memory wavefronts and shuffles per knot and sat at 63 % of the LSU data pipe (profiles/r02_k5_*).
 //
 // Iteration (same update order, exit rule |r^T P^-1 r| < exit_tol and 0-based iteration index as
 // src/gato_pcg.cuh:300-437; r^ = M r, p^ = M^-T p, so every scalar equals the reference's in exact arithmetic):
@@ -20,8 +23,11 @@
 #pragma once
 #include "gato_kernel_v2.cuh"
 
+#ifndef GATO_V5_PREFETCH
+#define GATO_V5_PREFETCH 0
+#endif
 #ifndef GATO_V5_CTAS
-#define GATO_V5_CTAS 2
+#define GATO_V5_CTAS 3
 #endif
 
 namespace gato {
@@ -30,13 +36,16 @@ template <int S, int C, int NT>
 __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveParams2 q) {
     using L = Layout2<S, C>;
     using SL = ScaledLayout<S, C>;
-    using MC = MapControl<S, C>;
-    constexpr int LPK = L::LPK, OWN = L::OWN, OWNC = L::OWNC, H = L::H, R = L::R, VS = L::VS, HALFP = L::HALFP,
-                  HALFU = L::HALFU, LDC = L::LDC;
-    static_assert(H == 2 && LPK == 4 && R == 7 && HALFU == 7 && OWN == 4 && HALFP == 8 && L::VEC_OWN,
-                  "the half-swapped vector loads below are written for S = 14");
-    constexpr int NW = NT / 32, NKP = NW * L::KPW, NW4 = (NW + 3) / 4;
-    constexpr int XS = (NKP + 2) * VS;
+    constexpr int VS = L::VS, HALFP = L::HALFP, HALFU = L::HALFU, LDC = L::LDC;
+    static_assert(L::H == 2 && HALFP == 8 && HALFU == 7, "the two 128-bit loads per half-slot below are written for S = 14");
+    constexpr int HU = HALFU;                // rows per lane, and columns per half
+    constexpr int NW = NT / 32, NKP = NT / 2, NW4 = (NW + 3) / 4;
+    // An iterate is stored as TWO arrays, one per half of the knots' entries ([slot][HALFP] each, knot k at slot k + 1),
+    // the second 16 bytes further round the banks: the two lanes of a knot read different halves in the same
+    // instruction, and with the halves interleaved in one array every 128-bit access was a 2-way bank conflict.
+    constexpr int XH = (NKP + 2) * HALFP;
+    constexpr int XS = 2 * XH + 4;
+    constexpr int CU = (C + 1) / 2;          // control rows per lane in the dz phase
     extern __shared__ __align__(16) float smem[];
     const SolveParams& p = q.p;
     const int K = p.K;
@@ -51,22 +60,17 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
     constexpr int NFLOATS = 4 * XS + NKP * (VS + LDC) + 64;
 
     const int tid = (int)threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int lik = lane % LPK, b = warp * L::KPW + lane / LPK;
+    const int b = tid >> 1, g = tid & 1;                  // knot, row half
     const bool active = b < K;
-    const int h = lik % H, g = lik / H;
-    const int po0 = g * HALFP + h * OWN;                  // first of this lane's OWN consecutive positions
-    bool ovr[OWN];
-    int orow[OWN];
-#pragma unroll
-    for (int j = 0; j < OWN; ++j) {
-        ovr[j] = L::own_valid(lik, j);
-        orow[j] = ovr[j] ? L::own_row(lik, j) : 0;
-    }
-    auto ld4 = [](const float* a, float (&v)[4]) {
-        const float4 t = *reinterpret_cast<const float4*>(a);
-        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    auto half = [](float* x, int slot, int hh) { return x + hh * (XH + 4) + slot * HALFP; };   // HU entries + a zero pad
+    auto ld8 = [](const float* a, float (&v)[8]) {
+        const float4 t0 = reinterpret_cast<const float4*>(a)[0], t1 = reinterpret_cast<const float4*>(a)[1];
+        v[0] = t0.x; v[1] = t0.y; v[2] = t0.z; v[3] = t0.w; v[4] = t1.x; v[5] = t1.y; v[6] = t1.z; v[7] = t1.w;
     };
-    auto st4 = [](float* a, const float (&v)[4]) { *reinterpret_cast<float4*>(a) = make_float4(v[0], v[1], v[2], v[3]); };
+    auto st8 = [](float* a, const float (&v)[8]) {
+        reinterpret_cast<float4*>(a)[0] = make_float4(v[0], v[1], v[2], v[3]);
+        reinterpret_cast<float4*>(a)[1] = make_float4(v[4], v[5], v[6], v[7]);
+    };
     // row `row` of a [.][VS] matrix in pos layout -> registers indexed by true column
     auto load_row = [&](const float* rowbase, float (&v)[S]) {
 #pragma unroll
@@ -78,19 +82,6 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                 if (L::pos_valid(4 * ci + u)) v[L::pos_row(4 * ci + u)] = e[u];
         }
     };
-    // reduce-scatter of R partial sums over the two lanes of a pair (lane ^ mask): the lane with flag = 0 ends with
-    // entries [0, OWN), its partner with [OWN, R) (+ a zero pad); the partner's registers are half-swapped
-    auto scatter = [&](const float (&acc)[R], float (&out)[OWN], int flag, int mask) {
-#pragma unroll
-        for (int j = 0; j < OWN; ++j) {
-            if (OWN + j < R) {
-                out[j] = acc[j] + __shfl_xor_sync(0xffffffffu, acc[OWN + j], mask);
-            } else {
-                const float recv = __shfl_xor_sync(0xffffffffu, acc[j], mask);
-                out[j] = flag ? 0.f : acc[j] + recv;
-            }
-        }
-    };
 
 #pragma unroll 1
     for (int sys = (int)blockIdx.x; sys < p.nsys; sys += (int)gridDim.x) {
@@ -100,110 +91,128 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
             float4* s4 = reinterpret_cast<float4*>(smem);
             for (int i = tid; i < NFLOATS / 4; i += NT) s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        float psi[R][HALFU];
+        // psi[i][c']: row g HU + i, column order [own half g | other half] (so the lane keeps the first HU partial
+        // sums of w and sends the last HU, whatever g)
+        float psi[HU][2 * HU];
         {
+            const float4* src = reinterpret_cast<const float4*>(kg + SL::oPSI + g * SL::PSIL);
             float raw[SL::PSIL];
-            const float4* src = reinterpret_cast<const float4*>(kg + SL::oPSI + lik * SL::PSIL);
 #pragma unroll
             for (int e = 0; e < SL::PSIL / 4; ++e) {
                 const float4 t = active ? __ldcg(src + e) : make_float4(0.f, 0.f, 0.f, 0.f);
                 raw[4 * e] = t.x; raw[4 * e + 1] = t.y; raw[4 * e + 2] = t.z; raw[4 * e + 3] = t.w;
             }
 #pragma unroll
-            for (int i = 0; i < R; ++i)
+            for (int i = 0; i < HU; ++i)
 #pragma unroll
-                for (int j = 0; j < HALFU; ++j) psi[i][j] = raw[i * HALFU + j];
+                for (int c = 0; c < 2 * HU; ++c)   // column c of the lane's order = block c / HU, column c % HU of it
+                    psi[i][c] = raw[(c / HU) * SL::PSIB + i * HU + c % HU];
         }
-        float lam[OWN], rr[OWN], pp[OWN];
+        if (GATO_V5_PREFETCH && active) {   // what the dz phase will read (A, B, R^-1, q, r, M; Q^-1 unless diagonal): start it towards L2 now
+            const char* kb = reinterpret_cast<const char*>(kg);
+            auto pf = [&](int lo, int hi) {   // float offsets; the two lanes of the knot take alternate 128-byte lines
+                for (int o = lo * 4 + g * 128; o < hi * 4; o += 256) asm volatile("prefetch.global.L2 [%0];" ::"l"(kb + o));
+            };
+            pf(L::oA, L::oQ);
+            if (!q.g_diag) pf(L::oQ, L::oR);
+            pf(L::oR, SL::REG);
+            pf(SL::oM, SL::oGAM);
+        }
+        float lam[8], rr[8], pp[8];   // entry 7 is the pad: always zero
         {
-            const float4 t = active ? __ldcg(reinterpret_cast<const float4*>(kg + SL::oGAM + po0)) : make_float4(0.f, 0.f, 0.f, 0.f);
-            rr[0] = t.x; rr[1] = t.y; rr[2] = t.z; rr[3] = t.w;     // pad positions hold zeros
-        }
+            float t[8];
+            if (active) {
+                const float4 t0 = __ldcg(reinterpret_cast<const float4*>(kg + SL::oGAM + g * HALFP));
+                const float4 t1 = __ldcg(reinterpret_cast<const float4*>(kg + SL::oGAM + g * HALFP) + 1);
+                t[0] = t0.x; t[1] = t0.y; t[2] = t0.z; t[3] = t0.w; t[4] = t1.x; t[5] = t1.y; t[6] = t1.z; t[7] = t1.w;
+            } else {
 #pragma unroll
-        for (int j = 0; j < OWN; ++j) lam[j] = 0.f;
+                for (int j = 0; j < 8; ++j) t[j] = 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { rr[j] = t[j]; lam[j] = 0.f; pp[j] = 0.f; }
+        }
         __syncthreads();
 
-        float* xp_k = xp + (b + 1) * VS + po0;
-        float* xr_k = xr + (b + 1) * VS + po0;
-        // u = psi_b x_{b-1} (own rows, combined over the column halves) and this lane's slice of w = psi_b^T x_b, which
-        // goes to the LEFT knot's slot of xw
-        auto apply = [&](const float* x, float* xw, float (&uo)[OWN]) {
-            const float* xl = x + b * VS + h * HALFP;           // knot b - 1, column half h
-            const float* xo = x + (b + 1) * VS + g * HALFP;     // own knot, row half g
-            float P[4], Q[4], P2[4], Q2[4];
-            ld4(xl + (g ? 4 : 0), P);
-            ld4(xl + (g ? 0 : 4), Q);
-            ld4(xo + (h ? 4 : 0), P2);
-            ld4(xo + (h ? 0 : 4), Q2);
-            const float eL[HALFU] = {P[0], P[1], P[2], g ? Q[3] : P[3], Q[0], Q[1], Q[2]};
-            const float eO[R] = {P2[0], P2[1], P2[2], h ? Q2[3] : P2[3], Q2[0], Q2[1], Q2[2]};
-            float u[R], w[HALFU];
+        float* xp_k = half(xp, b + 1, g);
+        float* xr_k = half(xr, b + 1, g);
+        // u = psi_b x_{b-1} (this lane's rows, complete) and the lane pair's w = psi_b^T x_b, of which this lane keeps
+        // the half g and stores it into the LEFT knot's slot of xw.  `own` = this lane's entries of x_b.
+        // (Packed FP32 FMAs -- fma.rn.f32x2, pairs along the columns -- were measured here too: 196 FFMA2 instead of
+        // 392 FFMA per iteration, but ~250 MOVs to form and split the pairs; 3.45 vs 3.50 ms per 8192 systems, not kept.)
+        auto apply = [&](float* x, const float (&own)[8], float* xw, float (&u)[8]) {
+            float e0[8], e1[8];
+            ld8(half(x, b, g), e0);                             // knot b - 1 (slot b), its half g: columns [0, HU) of psi
+            ld8(half(x, b, 1 - g), e1);                         // its other half
+            float w[2 * HU];
 #pragma unroll
-            for (int i = 0; i < R; ++i) u[i] = 0.f;
+            for (int i = 0; i < HU; ++i) u[i] = 0.f;
+            u[7] = 0.f;
 #pragma unroll
-            for (int j = 0; j < HALFU; ++j) w[j] = 0.f;
+            for (int c = 0; c < 2 * HU; ++c) w[c] = 0.f;
 #pragma unroll
-            for (int i = 0; i < R; ++i)
+            for (int i = 0; i < HU; ++i)
 #pragma unroll
-                for (int j = 0; j < HALFU; ++j) {
-                    u[i] = fmaf(psi[i][j], eL[j], u[i]);
-                    w[j] = fmaf(psi[i][j], eO[i], w[j]);
+                for (int c = 0; c < 2 * HU; ++c) {
+                    u[i] = fmaf(psi[i][c], c < HU ? e0[c] : e1[c - HU], u[i]);
+                    w[c] = fmaf(psi[i][c], own[i], w[c]);
                 }
-            float wo[OWN];
-            scatter(u, uo, h, 1);
-            scatter(w, wo, g, 2);
-            if (active) st4(xw + b * VS + h * HALFP + g * OWN, wo);
+            float wo[8];
+#pragma unroll
+            for (int j = 0; j < HU; ++j) wo[j] = w[j] + __shfl_xor_sync(0xffffffffu, w[HU + j], 1);
+            wo[7] = 0.f;
+            if (active) st8(half(xw, b, g), wo);                // knot b - 1 sits at slot b
         };
 
         // r~0 = r - O^ r, eta = r.r~0, p = r~0
-        if (active) st4(xr_k, rr);
+        if (active) st8(xr_k, rr);
         __syncthreads();
-        float uo[OWN], wv[OWN];
-        apply(xr, xwr, uo);
+        float uo[8], wv[8];
+        apply(xr, rr, xwr, uo);
         {
             float part = 0.f;
 #pragma unroll
-            for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
+            for (int j = 0; j < HU; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
             part = warp_sum32(part);
             if (lane == 0) redB[warp] = part;
         }
         __syncthreads();
         float eta = block_partials_sum(redB, NW4);
-        ld4(xwr + (b + 1) * VS + po0, wv);
+        ld8(half(xwr, b + 1, g), wv);
 #pragma unroll
-        for (int j = 0; j < OWN; ++j) pp[j] = (rr[j] - uo[j]) - wv[j];
-        if (active) st4(xp_k, pp);
+        for (int j = 0; j < HU; ++j) pp[j] = (rr[j] - uo[j]) - wv[j];
+        if (active) st8(xp_k, pp);
         __syncthreads();
 
         int iters = p.max_iters;
         float eta_last = eta;
         for (int it = 0; it < p.max_iters; ++it) {
-            apply(xp, xwp, uo);
+            apply(xp, pp, xwp, uo);
             {
                 float part = 0.f;
 #pragma unroll
-                for (int j = 0; j < OWN; ++j) part = fmaf(pp[j], fmaf(2.f, uo[j], pp[j]), part);
+                for (int j = 0; j < HU; ++j) part = fmaf(pp[j], fmaf(2.f, uo[j], pp[j]), part);
                 part = warp_sum32(part);
                 if (lane == 0) redA[warp] = part;
             }
             __syncthreads();
             const float v = block_partials_sum(redA, NW4);
             const float alpha = fast_div(eta, v);
-            ld4(xwp + (b + 1) * VS + po0, wv);
+            ld8(half(xwp, b + 1, g), wv);
 #pragma unroll
-            for (int j = 0; j < OWN; ++j) {
+            for (int j = 0; j < HU; ++j) {
                 const float ups = (pp[j] + uo[j]) + wv[j];
                 lam[j] = fmaf(alpha, pp[j], lam[j]);
                 rr[j] = fmaf(-alpha, ups, rr[j]);
             }
-            if (active) st4(xr_k, rr);
+            if (active) st8(xr_k, rr);
             const float eta_seed = rcp_seed(eta);
             __syncthreads();
-            apply(xr, xwr, uo);
+            apply(xr, rr, xwr, uo);
             {
                 float part = 0.f;
 #pragma unroll
-                for (int j = 0; j < OWN; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
+                for (int j = 0; j < HU; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
                 part = warp_sum32(part);
                 if (lane == 0) redB[warp] = part;
             }
@@ -212,10 +221,10 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
             eta_last = eta_new;
             if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
             const float beta = fast_div_seeded(eta_new, eta, eta_seed);
-            ld4(xwr + (b + 1) * VS + po0, wv);
+            ld8(half(xwr, b + 1, g), wv);
 #pragma unroll
-            for (int j = 0; j < OWN; ++j) pp[j] = fmaf(beta, pp[j], (rr[j] - uo[j]) - wv[j]);
-            if (active) st4(xp_k, pp);
+            for (int j = 0; j < HU; ++j) pp[j] = fmaf(beta, pp[j], (rr[j] - uo[j]) - wv[j]);
+            if (active) st8(xp_k, pp);
             eta = eta_new;
             __syncthreads();
         }

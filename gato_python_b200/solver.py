@@ -24,7 +24,8 @@ SYMBOLS = [
     "gato_plan_create_blocks", "gato_solve_sequence",
     "gato_plan_destroy", "gato_plan_set_cluster", "gato_plan_get_cluster", "gato_plan_set_kernel", "gato_plan_set_pipeline", "gato_plan_set_staging", "gato_plan_set_zero_copy",
     "gato_plan_set_preconditioner", "gato_plan_get_preconditioner",
-    "gato_scaled_layout", "gato_scaled_debug", "gato_plan_set_scaled_chunk",
+    "gato_scaled_layout", "gato_scaled_debug", "gato_plan_set_scaled_chunk", "gato_plan_get_kernel_for",
+    "gato_plan_set_profiling", "gato_plan_last_profile", "gato_solve_batched_multi",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -69,6 +70,11 @@ def lib():
     L.gato_scaled_layout.argtypes = [C.c_void_p, _ip]
     L.gato_scaled_debug.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, C.c_float, _fp, _ll]
     L.gato_plan_set_scaled_chunk.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_get_kernel_for.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.gato_solve_batched_multi.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, _fp, _ll, _fp, _ll, _fp, _ll, _fp, _ll,
+                                           _fp, _ll, _fp, _fp, _ip, C.c_float, C.c_int, C.c_int, C.c_float, _fp]
+    L.gato_plan_set_profiling.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_last_profile.argtypes = [C.c_void_p, _fp, _fp, _ip]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
     L.gato_solve.argtypes = [C.c_void_p, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_float, C.c_int, C.c_int,
                              C.c_float, _ip, _fp]
@@ -106,6 +112,46 @@ def _f32(a, shape=None):
     return a
 
 
+class _DLDevice(C.Structure):
+    _fields_ = [("device_type", C.c_int), ("device_id", C.c_int)]
+
+
+class _DLDataType(C.Structure):
+    _fields_ = [("code", C.c_uint8), ("bits", C.c_uint8), ("lanes", C.c_uint16)]
+
+
+class _DLTensor(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("device", _DLDevice), ("ndim", C.c_int), ("dtype", _DLDataType),
+                ("shape", C.POINTER(C.c_int64)), ("strides", C.POINTER(C.c_int64)), ("byte_offset", C.c_uint64)]
+
+
+def _dlpack_as_cai(a, name, device):
+    """Read a DLPack tensor (an object with __dlpack__, or a "dltensor" PyCapsule) into the dict shape of
+    __cuda_array_interface__.  The capsule is not consumed: it stays owned by its producer and is released with it
+    (the caller keeps the tensor alive for the duration of the asynchronous call, as with any device pointer)."""
+    cap = a if type(a).__name__ == "PyCapsule" else a.__dlpack__()
+    api = C.pythonapi
+    api.PyCapsule_IsValid.argtypes = [C.py_object, C.c_char_p]
+    api.PyCapsule_IsValid.restype = C.c_int
+    api.PyCapsule_GetPointer.argtypes = [C.py_object, C.c_char_p]
+    api.PyCapsule_GetPointer.restype = C.c_void_p
+    if not api.PyCapsule_IsValid(cap, b"dltensor"):
+        raise TypeError(f"{name}: not an unconsumed DLPack capsule")
+    t = C.cast(api.PyCapsule_GetPointer(cap, b"dltensor"), C.POINTER(_DLTensor)).contents   # DLManagedTensor starts with it
+    if t.device.device_type not in (2, 13):          # kDLCUDA, kDLCUDAManaged
+        raise ValueError(f"{name}: DLPack tensor is not on a CUDA device (device_type {t.device.device_type})")
+    if t.device.device_type == 2 and t.device.device_id != device:
+        raise ValueError(f"{name}: DLPack tensor lives on cuda:{t.device.device_id}, the plan on cuda:{device}")
+    if t.dtype.lanes != 1 or (t.dtype.code, t.dtype.bits) not in ((2, 32), (0, 32)):
+        raise ValueError(f"{name}: DLPack dtype (code {t.dtype.code}, {t.dtype.bits} bits) is not float32 / int32")
+    shape = tuple(int(t.shape[i]) for i in range(t.ndim))
+    item = 4
+    strides = None if not t.strides else tuple(int(t.strides[i]) * item for i in range(t.ndim))
+    cai = {"data": (int(t.data or 0) + int(t.byte_offset), False), "shape": shape, "strides": strides,
+           "typestr": "<f4" if t.dtype.code == 2 else "<i4", "_keepalive": cap}
+    return cai
+
+
 def supported_sizes():
     buf = (C.c_int * 32)()
     n = lib().gato_supported_sizes(buf, 16)
@@ -114,6 +160,62 @@ def supported_sizes():
 
 def device_count():
     return lib().gato_device_count()
+
+
+class MultiPlan:
+    """One process driving several GPUs (SURVEY.md 8(e)): a Plan per device over the same sparsity pattern;
+    `solve_batched` cuts the batch into contiguous slices, one host thread per device, results gathered by each
+    device's own D2H into disjoint slices of ONE host buffer (gato_solve_batched_multi).  No collective."""
+
+    def __init__(self, S, C_, K, G_row, G_col, C_row, C_col, devices=None, max_batch=1):
+        devices = list(range(device_count())) if devices is None else list(devices)
+        if not devices:
+            raise GatoError("no CUDA device")
+        self.plans = [Plan(S, C_, K, G_row, G_col, C_row, C_col, device=d, max_batch=max_batch) for d in devices]
+        self.devices = devices
+        p0 = self.plans[0]
+        self.S, self.C, self.K, self.n_z, self.n_l, self.nnzG, self.nnzC = p0.S, p0.C, p0.K, p0.n_z, p0.n_l, p0.nnzG, p0.nnzC
+
+    def solve_batched(self, G_val, C_val, g, c, lambda_in=None, exit_tol=1e-6, max_iters=500, warm_start=WARM_OFF,
+                      rho=0.0, out=None):
+        """Same arguments and results as Plan.solve_batched; device_ms is the longest device time."""
+        g = np.ascontiguousarray(g, np.float32)
+        if g.ndim != 2 or g.shape[1] != self.n_z:
+            raise ValueError(f"g must be [nsys, {self.n_z}]")
+        nsys = g.shape[0]
+
+        def prep(a, n):
+            a = np.ascontiguousarray(a, np.float32)
+            if a.ndim == 1:
+                a = a[None]
+            if a.shape[1] != n or a.shape[0] not in (1, nsys):
+                raise ValueError(f"expected [{nsys} or 1, {n}], got {a.shape}")
+            return a, (0 if (a.shape[0] == 1 and nsys > 1) else n)
+
+        G_val, ldG = prep(G_val, self.nnzG)
+        C_val, ldC = prep(C_val, self.nnzC)
+        c, ldc = prep(c, self.n_l)
+        lam_in, ldl = (prep(lambda_in, self.n_l) if lambda_in is not None else (None, 0))
+        if out is None:
+            out = (np.empty((nsys, self.n_l), np.float32), np.empty((nsys, self.n_z), np.float32),
+                   np.empty(nsys, np.int32))
+        lam, dz, iters = out
+        for a, shp, dt in ((lam, (nsys, self.n_l), np.float32), (dz, (nsys, self.n_z), np.float32),
+                           (iters, (nsys,), np.int32)):
+            if a.shape != shp or a.dtype != dt or not a.flags.c_contiguous:
+                raise ValueError(f"out array must be C-contiguous {shp} {np.dtype(dt).name}")
+        handles = (C.c_void_p * len(self.plans))(*[p._h.value for p in self.plans])
+        ms = C.c_float()
+        _check(lib().gato_solve_batched_multi(handles, len(self.plans), nsys, _f(G_val), ldG, _f(C_val), ldC, _f(g),
+                                              self.n_z, _f(c), ldc, _f(lam_in) if lam_in is not None else None, ldl,
+                                              _f(lam), _f(dz), _i(iters), exit_tol, int(max_iters), int(warm_start),
+                                              rho, C.byref(ms)))
+        return lam, dz, iters, ms.value
+
+    def close(self):
+        for p in self.plans:
+            p.close()
+        self.plans = []
 
 
 class Plan:
@@ -192,6 +294,19 @@ class Plan:
     def preconditioner(self):
         return int(lib().gato_plan_get_preconditioner(self._h))
 
+    def kernel_for(self, nsys, warm_start=WARM_OFF):
+        """The kernel a call with `nsys` systems runs (automatic selection picks kernel 5 for device-filling batches)."""
+        return int(lib().gato_plan_get_kernel_for(self._h, int(nsys), int(warm_start)))
+
+    def set_profiling(self, on):
+        _check(lib().gato_plan_set_profiling(self._h, int(bool(on))))
+
+    def last_profile(self):
+        """Kernel 5: (first-half ms, second-half ms, launches) of the last call made with profiling on."""
+        a, b, n = C.c_float(), C.c_float(), C.c_int()
+        _check(lib().gato_plan_last_profile(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        return a.value, b.value, n.value
+
     def set_scaled_chunk(self, systems_per_chunk):
         """Kernel 5: systems per pass through its scratch buffer (0 = automatic)."""
         _check(lib().gato_plan_set_scaled_chunk(self._h, int(systems_per_chunk)))
@@ -212,15 +327,13 @@ class Plan:
         pos = [(r // HU) * HALFP + r % HU for r in range(S)]
         M = raw[:, oM:oM + S * VS].reshape(K, S, VS)[:, :, pos]
         gam = raw[:, oGAM:oGAM + VS][:, pos]
-        OWN = (HU + 1) // 2
-        hs = [i + OWN if i + OWN < HU else (i - OWN if i >= OWN else i) for i in range(HU)]
         psi = np.zeros((K, S, S), np.float32)
-        for lik in range(4):
-            gg, hh = lik // 2, lik % 2
-            blk = raw[:, oPSI + lik * PSIL: oPSI + lik * PSIL + HU * HU].reshape(K, HU, HU)
-            for i in range(HU):
-                for j in range(HU):
-                    psi[:, gg * HU + (hs[i] if hh else i), hh * HU + (hs[j] if gg else j)] = blk[:, i, j]
+        PSIB = PSIL // 2
+        for gg in range(2):          # lane g: two row-major HU x HU blocks, [column half g | other half]
+            for s_ in range(2):
+                o = oPSI + gg * PSIL + s_ * PSIB
+                hh = gg if s_ == 0 else 1 - gg
+                psi[:, gg * HU:(gg + 1) * HU, hh * HU:(hh + 1) * HU] = raw[:, o:o + HU * HU].reshape(K, HU, HU)
         return dict(psi=psi, M=M, gamma_hat=gam, region=raw[:, :REG])
 
     def cluster(self):
@@ -341,8 +454,10 @@ class Plan:
         synchronised: this is `gato_solve_batched_device` for callers that hold framework tensors."""
         def ptr(a, dtype, name):
             cai = getattr(a, "__cuda_array_interface__", None)
+            if cai is None and (hasattr(a, "__dlpack__") or type(a).__name__ == "PyCapsule"):
+                cai = _dlpack_as_cai(a, name, self.device)      # DLPack producers and raw "dltensor" capsules
             if cai is None:
-                raise TypeError(f"{name} does not expose __cuda_array_interface__")
+                raise TypeError(f"{name} exposes neither __cuda_array_interface__ nor __dlpack__")
             if np.dtype(cai["typestr"]) != np.dtype(dtype):
                 raise ValueError(f"{name} must be {np.dtype(dtype).name}, got {np.dtype(cai['typestr']).name}")
             if cai.get("strides") is not None:

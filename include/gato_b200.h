@@ -176,6 +176,18 @@ int gato_solve_batched_device(gato_plan* plan, int nsys,
 int gato_unpack(gato_plan* plan, const float* G_val, const float* C_val, float rho,
                 float* G_dense_out, float* C_dense_out);
 
+/* One process, several GPUs (batches shard, no collective).  plans[i] must have been created for the
+ * same problem on ndev distinct devices.  The batch is cut into contiguous slices, one host thread per device runs
+ * gato_solve_batched on its slice of the caller's host arrays (a shared array, ld == 0, is read by every device), and
+ * the results land in disjoint slices of lambda_out / dz_out / iters_out: the only "gather" is each device's own D2H.
+ * device_ms_out receives the longest device time.  Replaces the reference's single-device assumption
+ * (src/gato_utils.cuh:831, include/gato_defines.h:22). */
+int gato_solve_batched_multi(gato_plan* const* plans, int ndev, int nsys, const float* G_val, long long ldG,
+                             const float* C_val, long long ldC, const float* g, long long ldg, const float* c,
+                             long long ldc, const float* lambda_in, long long ldl, float* lambda_out, float* dz_out,
+                             int* iters_out, float exit_tol, int max_iters, int warm_start, float rho,
+                             float* device_ms_out);
+
 /* Kernel 5 ("scaled system", gato_plan_set_kernel(plan, 5); STATE_SIZE = 14, K <= 56): the hot path as TWO kernels.
  * The first forms the reference's Schur blocks theta_b, phi_b, gamma_b (src/gato_schur.cuh:13-494) and, in FP64, the
  * congruence S^ = M S M^T (theta_b = L_b L_b^T, M_b = L_b^-1) whose diagonal blocks are the identity; the second runs
@@ -188,9 +200,17 @@ int gato_unpack(gato_plan* plan, const float* G_val, const float* C_val, float r
  * (parity hook for psi, M, gamma^); gato_plan_set_scaled_chunk: systems per pass through the scratch buffer
  * (0 = automatic: two per SM, which keeps the scratch in L2). */
 int gato_scaled_layout(const gato_plan* plan, int* layout8);
+/* the kernel a call with `nsys` systems and this warm_start runs (automatic selection: kernel 5 for batches of at
+ * least one system per SM when it holds the problem, else what gato_plan_get_kernel reports) */
+int gato_plan_get_kernel_for(const gato_plan* plan, int nsys, int warm_start);
 int gato_scaled_debug(gato_plan* plan, const float* G_val, const float* C_val, const float* g, const float* c,
                       float rho, float* scratch_out, long long nfloats);
 int gato_plan_set_scaled_chunk(gato_plan* plan, int systems_per_chunk);
+/* Kernel 5 launches two kernels per chunk; with profiling on, CUDA events are recorded on the launching stream
+ * around each of them, and gato_plan_last_profile returns the device time of each half summed over the chunks of the
+ * last call (it waits for that call's last event) and the number of kernel launches the call made. */
+int gato_plan_set_profiling(gato_plan* plan, int on);
+int gato_plan_last_profile(gato_plan* plan, float* first_half_ms, float* second_half_ms, int* launches);
 
 /* Solve one system and also return the Schur-phase intermediates in the reference's device layout
  * and (negated) storage signs: S_out, Pinv_out 3*S^2*K floats (gpu_library.cu:40-41), gamma_out

@@ -29,7 +29,7 @@ def run(lam, dz, its):
                             exit_tol=b["exit_tol"], max_iters=b["max_iters"], rho=b["rho"], stream=st.cuda_stream)
 
 
-for kernel, chunk in ((2, 0), (5, 0), (5, 148), (5, 592), (5, 1184), (5, 2368), (5, 8192)):
+for kernel, chunk in ((2, 0), (5, 0), (5, 148), (5, 1184), (5, 4096), (5, 8192)):
     pl.set_kernel(kernel)
     if kernel == 5:
         pl.set_scaled_chunk(chunk)

@@ -271,9 +271,11 @@ def test_batched_pipeline_is_bitwise_equal():
     pl.close()
 
 
-def test_full_size_batch_properties():
+@pytest.mark.parametrize("kernel", [2, 5], ids=["onecta", "scaled"])
+def test_full_size_batch_properties(kernel):
     """BASELINE.json configs[3] at full size (8192 systems): size-independent properties -- the KKT
-    residual of every system in FP64, and equality with per-system solves on a sample."""
+    residual of every system in FP64, and equality with per-system solves on a sample (same kernel: a batch of
+    this size selects kernel 5 automatically, a single solve the one-CTA kernel)."""
     from gato_python_b200.problems import iiwa_like
     base = iiwa_like(K=50, seed=1000)
     n = 8192
@@ -282,6 +284,8 @@ def test_full_size_batch_properties():
     c = (0.01 * rng.standard_normal((n, base["c"].size))).astype(np.float32)
     c[:, :14] = 0
     pl = plan_of(base)
+    assert pl.kernel_for(n) == 5 and pl.kernel_for(1) == 2 and pl.kernel_for(n, WARM_TRUE) == 2
+    pl.set_kernel(kernel)
     lam, dz, iters, ms = pl.solve_batched(base["G_val"], base["C_val"], g, c, None, base["exit_tol"],
                                           base["max_iters"], 0, base["rho"])
     assert iters.min() > 0 and iters.max() < base["max_iters"]
