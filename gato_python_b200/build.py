@@ -38,7 +38,7 @@ def _stale(target, sources):
 
 def _lib_sources():
     srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))
-            if f.endswith((".cu", ".cuh", ".inc", ".h")) and f not in ("floors.cu", "gpu_library.cu")]
+            if f.endswith((".cu", ".cuh", ".inc", ".h")) and f not in ("floors.cu", "gpu_library.cu", "tf32_experiment.cu")]
     srcs.append(os.path.join(ROOT, "include", "gato_b200.h"))
     return srcs
 
@@ -117,12 +117,23 @@ def build_floors(force=False):
     return out
 
 
+def build_tf32_experiment(force=False):
+    """build/tf32_experiment: the tensor-core option for the Schur GEMMs, timed and error-checked (csrc/tf32_experiment.cu)."""
+    src = os.path.join(CSRC, "tf32_experiment.cu")
+    out = os.path.join(ROOT, "build", "tf32_experiment")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    if force or _stale(out, [src]):
+        subprocess.run([_nvcc()] + ARCH + ["-O3", "-std=c++17", "-lineinfo", src, "-o", out], check=True)
+    return out
+
+
 DEFAULT_MODULES = [(2, 1, 5), (14, 7, 50), (14, 7, 256)]
 
 
 def build_all(force=False):
     build_library(force=force)
     build_floors(force=force)
+    build_tf32_experiment(force=force)
     return [build_module(S, C, K, force=force) for (S, C, K) in DEFAULT_MODULES]
 
 

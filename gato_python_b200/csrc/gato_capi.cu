@@ -360,7 +360,10 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
         return fail(GATO_EUNSUPPORTED, "kernel 5 has no true warm start yet (use kernel 2 for GATO_WARM_TRUE)");
     const long long per = v5_scratch_per_system<S, C>(pl);
     const int sms = pl->sm_count > 0 ? pl->sm_count : 148;
-    int chunk = pl->v5_chunk > 0 ? pl->v5_chunk : 16 * sms;   // measured: larger chunks win although the scratch then leaves L2
+    // measured (profiles/r02_k5_chunk_sweep.json): larger chunks win although the scratch then leaves L2 -- the tail of
+    // each second-half launch (iteration counts differ between systems) costs more than the DRAM round trip
+    int chunk = pl->v5_chunk > 0 ? pl->v5_chunk : 64 * sms;
+    (void)sms;
     if (chunk > q.p.nsys) chunk = q.p.nsys;
     int si = 0;
     while (si < pl->nscr && pl->scr_stream[si] != st) ++si;

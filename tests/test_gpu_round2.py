@@ -464,3 +464,35 @@ def test_dlpack_inputs():
     with pytest.raises((TypeError, ValueError)):
         pl.solve_batched_cuda(OnlyDLPack(ins[0].cpu()), *ins[1:], lam, dz, it)
     pl.close()
+
+
+def test_cmake_built_module_runs_the_reference_pendulum_test():
+    """The reference's build entry (`cmake .. -DS=2 -DC=1 -DK=5 && make`, CMakeLists.txt:17-26 / install.bash) produces a
+    `gpu_library` module; it is driven exactly like the reference's own test_pendulum_5.py:9-37 drives the reference
+    module (lists in, positional arguments, testiters = 10) and checked with that test's dense-KKT assertion."""
+    import subprocess
+    bdir = os.path.join(ROOT, "build", "cmake_S2_C1_K5")
+    if not (os.path.isdir(bdir) and any(f.startswith("gpu_library") for f in os.listdir(bdir))):
+        pytest.skip("cmake build of the pendulum module not present (__graft_entry__.build() makes it)")
+    code = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[2])
+import gpu_library
+from gato_python_b200.problems import pendulum5
+p = pendulum5()
+L = lambda k: p[k].tolist()
+l, dz = gpu_library.linsys_solve(L("G_row"), L("G_col"), L("G_val"), L("C_row"), L("C_col"), L("C_val"), L("g"),
+                                 [0] * 10, [0.] * 10, 10, 1e-6, 10, False, .001)
+from scipy import sparse
+G = sparse.csr_matrix((p["G_val"], p["G_col"], p["G_row"])).todense()
+Cm = sparse.csr_matrix((p["C_val"], p["C_col"], p["C_row"])).todense()
+A = np.block([[G, Cm.T], [Cm, np.zeros((10, 10))]])
+x = np.linalg.inv(A).dot(np.concatenate([p["g"], np.zeros(10)]).reshape(-1, 1))
+x_gato = np.concatenate([dz, l]).reshape(-1, 1)
+assert isinstance(l, list) and isinstance(dz, list) and len(l) == 10 and len(dz) == 14
+assert np.allclose(x_gato, x, rtol=1, atol=0.01)
+print("Test passed")
+"""
+    r = subprocess.run([sys.executable, "-c", code, bdir, ROOT], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "Test passed" in r.stdout, (r.stdout[-500:], r.stderr[-1500:])
+    assert "first run PCG terminated in" in r.stdout and "avg time:" in r.stdout      # the reference's two summary lines
