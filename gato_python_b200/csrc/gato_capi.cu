@@ -334,7 +334,7 @@ int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st
     if constexpr (HasV5<S>::value) {
         using L = gato::Layout2<S, C>;
         constexpr int NT = kV5Threads, NKP = NT / 2;
-        constexpr size_t smem = (size_t)(4 * (2 * (NKP + 2) * L::HALFP + 4) + NKP * (L::VS + L::LDC) + 64) * sizeof(float);
+        constexpr size_t smem = (size_t)(4 * (2 * (NKP + 2) * L::HALFP + 4) + NKP * (L::VS + L::LDC) + 64 + 4) * sizeof(float);
         auto kern = gato::gato_pcg_scaled<S, C, NT>;
         if (pl->occp_val == 0) {
             int occ = 0;
@@ -372,8 +372,9 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
             return fail(GATO_EUNSUPPORTED, "kernel 5 keeps one scratch buffer per stream: more than %d streams on one plan", gato_plan::kScr);
         pl->scr_stream[pl->nscr++] = st;
     }
-    GATO_CUDA(pl->dscr[si].ensure((size_t)chunk * (size_t)per * sizeof(float)));
+    GATO_CUDA(pl->dscr[si].ensure((size_t)chunk * (size_t)per * sizeof(float) + 256));
     q.scr = (float*)pl->dscr[si].p;
+    q.gbuf = q.scr + (size_t)chunk * (size_t)per;     // behind the scratch: the second half's work counter
     q.scr_ld = per;
     const gato::SolveParams base = q.p;
     const int nchunk = (base.nsys + chunk - 1) / chunk;

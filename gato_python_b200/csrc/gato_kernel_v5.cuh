@@ -32,6 +32,19 @@
 
 namespace gato {
 
+// Sum over the warp in THREE dependent shuffle steps instead of five (4-ary, 4-ary, 2-ary: seven shuffles): this kernel
+// waits on the dependent chain of the reduction, not on shuffle issue slots.  Every lane ends with the same bits
+// (each level adds the same pair sums, and a + b == b + a exactly).
+__device__ __forceinline__ float warp_sum32_3(float v) {
+    const float a1 = __shfl_xor_sync(0xffffffffu, v, 1), a2 = __shfl_xor_sync(0xffffffffu, v, 2),
+                a3 = __shfl_xor_sync(0xffffffffu, v, 3);
+    v = (v + a1) + (a2 + a3);
+    const float b1 = __shfl_xor_sync(0xffffffffu, v, 4), b2 = __shfl_xor_sync(0xffffffffu, v, 8),
+                b3 = __shfl_xor_sync(0xffffffffu, v, 12);
+    v = (v + b1) + (b2 + b3);
+    return v + __shfl_xor_sync(0xffffffffu, v, 16);
+}
+
 template <int S, int C, int NT>
 __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveParams2 q) {
     using L = Layout2<S, C>;
@@ -83,13 +96,21 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
         }
     };
 
+    // Systems are handed out by an atomic counter (reset by the first half, which always runs before this kernel on the
+    // same stream): iteration counts differ between systems, and a static split left the slowest CTA ~7 % behind.
+    int* next_sys = reinterpret_cast<int*>(smem + NFLOATS);
+    int* counter = reinterpret_cast<int*>(q.gbuf);
 #pragma unroll 1
-    for (int sys = (int)blockIdx.x; sys < p.nsys; sys += (int)gridDim.x) {
+    while (true) {
+        if (tid == 0) *next_sys = atomicAdd(counter, 1);
+        __syncthreads();
+        const int sys = *next_sys;
+        if (sys >= p.nsys) break;
         const float* scr = q.scr + (long long)sys * q.scr_ld;
         const float* kg = scr + (long long)(active ? b : 0) * SL::KSCR;     // this knot's scratch
         {   // halos, pads and the never-written slots must read as zero
             float4* s4 = reinterpret_cast<float4*>(smem);
-            for (int i = tid; i < NFLOATS / 4; i += NT) s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = tid; i < NFLOATS / 4; i += NT) s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);   // (not next_sys: behind NFLOATS)
         }
         // psi[i][c']: row g HU + i, column order [own half g | other half] (so the lane keeps the first HU partial
         // sums of w and sends the last HU, whatever g)
@@ -173,7 +194,7 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
             float part = 0.f;
 #pragma unroll
             for (int j = 0; j < HU; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
-            part = warp_sum32(part);
+            part = warp_sum32_3(part);
             if (lane == 0) redB[warp] = part;
         }
         __syncthreads();
@@ -192,7 +213,7 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                 float part = 0.f;
 #pragma unroll
                 for (int j = 0; j < HU; ++j) part = fmaf(pp[j], fmaf(2.f, uo[j], pp[j]), part);
-                part = warp_sum32(part);
+                part = warp_sum32_3(part);
                 if (lane == 0) redA[warp] = part;
             }
             __syncthreads();
@@ -213,7 +234,7 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                 float part = 0.f;
 #pragma unroll
                 for (int j = 0; j < HU; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
-                part = warp_sum32(part);
+                part = warp_sum32_3(part);
                 if (lane == 0) redB[warp] = part;
             }
             __syncthreads();

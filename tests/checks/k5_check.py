@@ -60,3 +60,28 @@ out["k5_vs_k2"] = {"max_rel_lambda": float(rl.max()), "mean_rel_lambda": float(r
 for key in ("k5_chunk148", "k5_chunk8192"):
     out[key]["bitwise_equal_to_default_chunk"] = bool(np.array_equal(res[key][0], l5) and np.array_equal(res[key][2], i5))
 print(json.dumps(out))
+
+# single-solve latency, kernel only (device buffers), kernel 2 vs kernel 5
+from gato_python_b200.problems import iiwa_like  # noqa: E402
+prob = iiwa_like(14, 7, 50, seed=0)
+p1 = Plan(14, 7, 50, prob["G_row"], prob["G_col"], prob["C_row"], prob["C_col"])
+t = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(dev)  # noqa: E731
+G, Cv, g1, c1 = t(prob["G_val"]), t(prob["C_val"]), t(prob["g"]), t(prob["c"])
+l1 = torch.empty(p1.n_l, device=dev); z1 = torch.empty(p1.n_z, device=dev); i1 = torch.empty(1, dtype=torch.int32, device=dev)
+single = {}
+for kernel in (2, 5):
+    p1.set_kernel(kernel)
+    def run1():
+        p1.solve_batched_device(1, G.data_ptr(), 0, Cv.data_ptr(), 0, g1.data_ptr(), 0, c1.data_ptr(), 0, l1.data_ptr(),
+                                z1.data_ptr(), i1.data_ptr(), exit_tol=prob["exit_tol"], max_iters=prob["max_iters"],
+                                rho=prob["rho"], stream=st.cuda_stream)
+    for _ in range(20):
+        run1()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(200):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); run1(); e1.record(); e1.synchronize()
+        ts.append(e0.elapsed_time(e1) * 1e3)
+    single[f"k{kernel}"] = {"kernel_us_median": float(np.median(ts)), "iters": int(i1.item())}
+print(json.dumps({"single_solve": single}))
