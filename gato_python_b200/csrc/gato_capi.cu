@@ -16,6 +16,7 @@
 #include "gato_kernels.cuh"
 #include "gato_kernel_v2.cuh"
 #include "gato_kernel_v5.cuh"
+#include "gato_kernel_v5_lat.cuh"
 
 #ifndef GATO_EXTRA_S
 #define GATO_EXTRA_S 0
@@ -112,6 +113,7 @@ struct gato_plan {
     cudaStream_t scr_stream[kScr] = {};
     int nscr = 0;
     int v5_chunk = 0;       // kernel 5: systems per chunk (0 = automatic)
+    int v5_variant = 0;     // kernel 5, second half: 0 = by call size, 1 = latency kernel (4 lanes per knot), 2 = throughput kernel
     int profile = 0;        // kernel 5: record CUDA events around each of its launches (gato_plan_set_profiling)
     std::vector<cudaEvent_t> prof_ev;   // 3 per chunk of the last profiled call: before first half | between | after second
     int prof_chunks = 0, prof_launches = 0;
@@ -131,6 +133,7 @@ struct gato_plan {
     mutable int occ_smem = -1, occ_val = 0;
     mutable int occ5_smem = -1, occ5_val = 0;   // the same for the first half of kernel 5
     mutable int occp_val = 0;                   // second half of kernel 5: resident CTAs per SM
+    mutable int occl_val = 0;                   // its latency variant
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -329,10 +332,36 @@ int launch_v5_first(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st)
     return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
 }
 
+// latency variant of the second half (four lanes per knot, seven warps per system): single solves and batches below
+// one system per SM
 template <int S, int C>
-int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
+int launch_v5_second_lat(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
     if constexpr (HasV5<S>::value) {
         using L = gato::Layout2<S, C>;
+        constexpr int NT = 224, NKP = (NT / 32) * L::KPW;
+        constexpr size_t smem = (size_t)(4 * (NKP + 2) * L::VS + NKP * (L::VS + L::LDC) + 64) * sizeof(float);
+        auto kern = gato::gato_pcg_scaled4<S, C, NT>;
+        if (pl->occl_val == 0) {
+            int occ = 0;
+            GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+            if (occ < 1) return fail(GATO_EUNSUPPORTED, "second half of kernel 5 does not fit an SM");
+            pl->occl_val = occ;
+        }
+        const int resident = pl->occl_val * (pl->sm_count > 0 ? pl->sm_count : 148);
+        const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
+        kern<<<grid, NT, smem, st>>>(q);
+        GATO_CUDA(cudaGetLastError());
+        return GATO_OK;
+    }
+    return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
+}
+
+template <int S, int C>
+int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st, bool lat) {
+    if constexpr (HasV5<S>::value) {
+        using L = gato::Layout2<S, C>;
+        if (lat) return launch_v5_second_lat<S, C>(pl, q, st);
         constexpr int NT = kV5Threads, NKP = NT / 2;
         constexpr size_t smem = (size_t)(4 * (2 * (NKP + 2) * L::HALFP + 4) + NKP * (L::VS + L::LDC) + 64 + 4) * sizeof(float);
         auto kern = gato::gato_pcg_scaled<S, C, NT>;
@@ -363,7 +392,6 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
     // measured (profiles/r02_k5_chunk_sweep.json): larger chunks win although the scratch then leaves L2 -- the tail of
     // each second-half launch (iteration counts differ between systems) costs more than the DRAM round trip
     int chunk = pl->v5_chunk > 0 ? pl->v5_chunk : 64 * sms;
-    (void)sms;
     if (chunk > q.p.nsys) chunk = q.p.nsys;
     int si = 0;
     while (si < pl->nscr && pl->scr_stream[si] != st) ++si;
@@ -378,6 +406,10 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
     q.scr_ld = per;
     const gato::SolveParams base = q.p;
     const int nchunk = (base.nsys + chunk - 1) / chunk;
+    // which second half: decided by the size of the whole call (every chunk of it runs the same kernel, so the result
+    // does not depend on the chunking); gato_plan_set_scaled_variant overrides
+    const int whole = pl->batch_hint > 0 ? pl->batch_hint : base.nsys;
+    const bool lat = 4 * pl->K <= 224 && (pl->v5_variant == 1 || (pl->v5_variant == 0 && whole < sms));
     const bool prof = pl->profile && !first_only;
     if (prof) {
         while ((int)pl->prof_ev.size() < 3 * nchunk) {
@@ -394,7 +426,7 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
         int rc = launch_v5_first<S, C>(pl, q, st);
         if (rc || first_only) return rc;
         if (prof) GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci + 1], st));
-        if ((rc = launch_v5_second<S, C>(pl, q, st))) return rc;
+        if ((rc = launch_v5_second<S, C>(pl, q, st, lat))) return rc;
         if (prof) { GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci + 2], st)); pl->prof_chunks = ci + 1; }
     }
     pl->prof_launches = 2 * nchunk;

@@ -26,6 +26,7 @@ SYMBOLS = [
     "gato_plan_set_preconditioner", "gato_plan_get_preconditioner",
     "gato_scaled_layout", "gato_scaled_debug", "gato_plan_set_scaled_chunk", "gato_plan_get_kernel_for",
     "gato_plan_set_profiling", "gato_plan_last_profile", "gato_solve_batched_multi",
+    "gato_plan_set_scaled_variant",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -73,6 +74,7 @@ def lib():
     L.gato_plan_get_kernel_for.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.gato_solve_batched_multi.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, _fp, _ll, _fp, _ll, _fp, _ll, _fp, _ll,
                                            _fp, _ll, _fp, _fp, _ip, C.c_float, C.c_int, C.c_int, C.c_float, _fp]
+    L.gato_plan_set_scaled_variant.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_profiling.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_last_profile.argtypes = [C.c_void_p, _fp, _fp, _ip]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
@@ -297,6 +299,10 @@ class Plan:
     def kernel_for(self, nsys, warm_start=WARM_OFF):
         """The kernel a call with `nsys` systems runs (automatic selection picks kernel 5 for device-filling batches)."""
         return int(lib().gato_plan_get_kernel_for(self._h, int(nsys), int(warm_start)))
+
+    def set_scaled_variant(self, variant):
+        """Kernel 5, second half: 0 = by call size, 1 = latency kernel (4 lanes per knot), 2 = throughput kernel."""
+        _check(lib().gato_plan_set_scaled_variant(self._h, int(variant)))
 
     def set_profiling(self, on):
         _check(lib().gato_plan_set_profiling(self._h, int(bool(on))))

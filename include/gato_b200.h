@@ -206,6 +206,11 @@ int gato_plan_get_kernel_for(const gato_plan* plan, int nsys, int warm_start);
 int gato_scaled_debug(gato_plan* plan, const float* G_val, const float* C_val, const float* g, const float* c,
                       float rho, float* scratch_out, long long nfloats);
 int gato_plan_set_scaled_chunk(gato_plan* plan, int systems_per_chunk);
+/* Kernel 5 has two second halves over the same scratch: a THROUGHPUT kernel (two lanes per knot, four warps per system,
+ * three systems per SM) and a LATENCY kernel (four lanes per knot, seven warps per system: a lone system iterates
+ * ~1.6 x faster).  0 = chosen by the size of the whole call (latency below one system per SM), 1 / 2 = forced.  The two
+ * agree within the rounding of their summation orders, not bit for bit. */
+int gato_plan_set_scaled_variant(gato_plan* plan, int variant);
 /* Kernel 5 launches two kernels per chunk; with profiling on, CUDA events are recorded on the launching stream
  * around each of them, and gato_plan_last_profile returns the device time of each half summed over the chunks of the
  * last call (it waits for that call's last event) and the number of kernel launches the call made. */

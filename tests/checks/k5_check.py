@@ -84,4 +84,15 @@ for kernel in (2, 5):
         e0.record(); run1(); e1.record(); e1.synchronize()
         ts.append(e0.elapsed_time(e1) * 1e3)
     single[f"k{kernel}"] = {"kernel_us_median": float(np.median(ts)), "iters": int(i1.item())}
+    if kernel == 5:
+        for variant in (1, 2):
+            p1.set_scaled_variant(variant)
+            p1.set_profiling(True)
+            hs = []
+            for _ in range(50):
+                run1()
+                hs.append(p1.last_profile()[:2])
+            p1.set_profiling(False)
+            single[f"k5_variant{variant}_halves_us"] = [float(np.median([h[0] for h in hs]) * 1e3), float(np.median([h[1] for h in hs]) * 1e3)]
+        p1.set_scaled_variant(0)
 print(json.dumps({"single_solve": single}))

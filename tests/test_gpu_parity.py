@@ -286,6 +286,8 @@ def test_full_size_batch_properties(kernel):
     pl = plan_of(base)
     assert pl.kernel_for(n) == 5 and pl.kernel_for(1) == 2 and pl.kernel_for(n, WARM_TRUE) == 2
     pl.set_kernel(kernel)
+    if kernel == 5:
+        pl.set_scaled_variant(2)      # single solves below would take the latency variant: keep the batch's kernel
     lam, dz, iters, ms = pl.solve_batched(base["G_val"], base["C_val"], g, c, None, base["exit_tol"],
                                           base["max_iters"], 0, base["rho"])
     assert iters.min() > 0 and iters.max() < base["max_iters"]

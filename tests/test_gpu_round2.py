@@ -337,6 +337,7 @@ def test_kernel5_batch_matches_single_and_oracle():
     assert np.array_equal(lam, lam2) and np.array_equal(dz, dz2) and np.array_equal(it, it2)
     p1 = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"])
     p1.set_kernel(5)
+    p1.set_scaled_variant(2)      # a single solve would take the latency variant of the second half: force the batch's
     for i in (0, 147, 148, 295, 296, 297, 500, 592, n - 1):
         l1, d1, i1 = gpu(p1, _sys_of(b, i))
         assert np.array_equal(l1, lam[i]) and np.array_equal(d1, dz[i]) and i1["iters"] == it[i], i
@@ -344,6 +345,15 @@ def test_kernel5_batch_matches_single_and_oracle():
         lam_o, dz_o, io = oracle(_sys_of(b, i))
         assert close(lam[i], lam_o) and close(dz[i], dz_o), (i, rel2(lam[i], lam_o))
         assert abs(int(it[i]) - io["iters"]) <= 1
+    # the latency variant of the second half: same solution within the rounding of its summation order
+    pl.set_scaled_variant(1)
+    lam5, dz5, it5, _ = pl.solve_batched(*args)
+    assert np.abs(it5.astype(int) - it.astype(int)).max() <= 1
+    assert max(rel2(lam5[i], lam[i]) for i in range(n)) < 2e-5 and max(rel2(dz5[i], dz[i]) for i in range(n)) < 2e-5
+    p1.set_scaled_variant(0)
+    l1, d1, i1 = gpu(p1, _sys_of(b, 5))                 # a single solve takes it on its own
+    assert np.array_equal(l1, lam5[5]) and np.array_equal(d1, dz5[5]) and i1["iters"] == it5[5]
+    pl.set_scaled_variant(0)
     # shared-matrix form (ld = 0) and the same results from the one-CTA kernel within the tolerance
     pl.set_scaled_chunk(0)
     lam3, dz3, it3, _ = pl.solve_batched(b["G_val"][0], b["C_val"][0], b["g"], b["c"], None, b["exit_tol"],
