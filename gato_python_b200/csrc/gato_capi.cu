@@ -673,13 +673,14 @@ bool v5_ok(const gato_plan* pl) {
     return false;
 }
 
-bool use_v5(const gato_plan* pl) { return pl->kernel == 5 && v5_ok(pl); }
+bool use_v5(const gato_plan* pl) { return pl->kernel == 5 && pl->precond == 0 && v5_ok(pl); }
 
 // automatic choice for a call of `nsys` systems: kernel 5 for batches that fill the device (its two kernels keep two to
 // three systems per SM in flight: measured 2.3 M vs 2.0 M solves/s at 8192 IIWA-50 systems), the one-CTA kernel for
 // single solves and small batches (one launch; the zero-copy single solve needs its TMA staging) and for true warm
 // starts, which kernel 5 does not implement
 bool use_v5_for(const gato_plan* pl, int nsys, int warm) {
+    if (pl->precond != 0) return false;      // kernel 5 is the stair preconditioner in scaled coordinates: block-Jacobi runs on kernels 1-4
     if (pl->kernel == 5) return v5_ok(pl);
     if (pl->kernel != 0 || pl->cl_override > 0 || warm == 2) return false;
     if (pl->batch_hint > 0) nsys = pl->batch_hint;

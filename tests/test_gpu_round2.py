@@ -115,6 +115,16 @@ def test_block_jacobi_preconditioner(name, kernel):
     pl.set_preconditioner("stair")
     lam2, _, info2 = gpu(pl, prob)
     assert np.array_equal(lam2, lam_s) and info2["iters"] == info_s["iters"]
+    if prob["S"] == 14 and prob["K"] <= 56:      # kernel 5 is stair-only: both orders of asking are refused
+        from gato_python_b200 import GatoError
+        pl.set_kernel(5)
+        with pytest.raises(GatoError):
+            pl.set_preconditioner(PRECOND_BLOCK_JACOBI)
+        pl.set_kernel(0)
+        pl.set_preconditioner(PRECOND_BLOCK_JACOBI)
+        assert pl.kernel_for(8192) != 5
+        with pytest.raises(GatoError):
+            pl.set_kernel(5)
     pl.close()
 
 
