@@ -675,7 +675,7 @@ bool v5_ok(const gato_plan* pl) {
 
 bool use_v5(const gato_plan* pl) { return pl->kernel == 5 && pl->precond == 0 && v5_ok(pl); }
 
-// automatic choice for a call of `nsys` systems: kernel 5 for batches that fill the device (its two kernels keep two to
+// automatic choice for a call of `nsys` systems: kernel 5 for batches that fill the device (>= two systems per SM) (its two kernels keep two to
 // three systems per SM in flight: measured 2.3 M vs 2.0 M solves/s at 8192 IIWA-50 systems), the one-CTA kernel for
 // single solves and small batches (one launch; the zero-copy single solve needs its TMA staging) and for true warm
 // starts, which kernel 5 does not implement
@@ -684,7 +684,7 @@ bool use_v5_for(const gato_plan* pl, int nsys, int warm) {
     if (pl->kernel == 5) return v5_ok(pl);
     if (pl->kernel != 0 || pl->cl_override > 0 || warm == 2) return false;
     if (pl->batch_hint > 0) nsys = pl->batch_hint;
-    return nsys >= (pl->sm_count > 0 ? pl->sm_count : 148) && v5_ok(pl);
+    return nsys >= 2 * (pl->sm_count > 0 ? pl->sm_count : 148) && v5_ok(pl);   // below two waves of the one-CTA kernel it is not ahead
 }
 
 long long v5_scratch_floats(const gato_plan* pl) {

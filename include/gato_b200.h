@@ -201,7 +201,7 @@ int gato_solve_batched_multi(gato_plan* const* plans, int ndev, int nsys, const 
  * (0 = automatic: two per SM, which keeps the scratch in L2). */
 int gato_scaled_layout(const gato_plan* plan, int* layout8);
 /* the kernel a call with `nsys` systems and this warm_start runs (automatic selection: kernel 5 for batches of at
- * least one system per SM when it holds the problem, else what gato_plan_get_kernel reports) */
+ * least two systems per SM when it holds the problem, else what gato_plan_get_kernel reports) */
 int gato_plan_get_kernel_for(const gato_plan* plan, int nsys, int warm_start);
 int gato_scaled_debug(gato_plan* plan, const float* G_val, const float* C_val, const float* g, const float* c,
                       float rho, float* scratch_out, long long nfloats);
