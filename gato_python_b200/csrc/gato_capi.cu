@@ -134,6 +134,8 @@ struct gato_plan {
     mutable int occ5_smem = -1, occ5_val = 0;   // the same for the first half of kernel 5
     mutable int occp_val = 0;                   // second half of kernel 5: resident CTAs per SM
     mutable int occl_val = 0;                   // its latency variant
+    mutable int occp_form = 0;
+    int pcg_form = 0;       // kernel 5, throughput second half: 0 = the reference's two reductions per iteration, 1 = single reduction
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -364,13 +366,14 @@ int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st
         if (lat) return launch_v5_second_lat<S, C>(pl, q, st);
         constexpr int NT = kV5Threads, NKP = NT / 2;
         constexpr size_t smem = (size_t)(4 * (2 * (NKP + 2) * L::HALFP + 4) + NKP * (L::VS + L::LDC) + 64 + 4) * sizeof(float);
-        auto kern = gato::gato_pcg_scaled<S, C, NT>;
-        if (pl->occp_val == 0) {
+        auto kern = pl->pcg_form == 1 ? gato::gato_pcg_scaled<S, C, NT, true> : gato::gato_pcg_scaled<S, C, NT, false>;
+        if (pl->occp_val == 0 || pl->occp_form != pl->pcg_form) {
             int occ = 0;
             GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
             if (occ < 1) return fail(GATO_EUNSUPPORTED, "second half of kernel 5 does not fit an SM");
             pl->occp_val = occ;
+            pl->occp_form = pl->pcg_form;
         }
         const int resident = pl->occp_val * (pl->sm_count > 0 ? pl->sm_count : 148);
         const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
@@ -400,7 +403,7 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
             return fail(GATO_EUNSUPPORTED, "kernel 5 keeps one scratch buffer per stream: more than %d streams on one plan", gato_plan::kScr);
         pl->scr_stream[pl->nscr++] = st;
     }
-    GATO_CUDA(pl->dscr[si].ensure((size_t)chunk * (size_t)per * sizeof(float) + 256));
+    GATO_CUDA(pl->dscr[si].ensure((size_t)chunk * (size_t)per * sizeof(float) + 4096));
     q.scr = (float*)pl->dscr[si].p;
     q.gbuf = q.scr + (size_t)chunk * (size_t)per;     // behind the scratch: the second half's work counter
     q.scr_ld = per;

@@ -30,6 +30,14 @@
 #define GATO_V5_CTAS 3
 #endif
 
+// Development builds (-DGATO_V5_TRACE): thread 0 of the CTA that takes system 0 stamps clock64() at eleven points of
+// each of the first 8 iterations into the buffer behind the work counter (tests/checks/k5_trace.py reads it).
+#ifdef GATO_V5_TRACE
+#define V5_STAMP(i) do { if (trace_on && it < 8) trace[it * 12 + (i)] = clock64(); } while (0)
+#else
+#define V5_STAMP(i) do { } while (0)
+#endif
+
 namespace gato {
 
 // Sum over the warp in THREE dependent shuffle steps instead of five (4-ary, 4-ary, 2-ary: seven shuffles): this kernel
@@ -45,7 +53,8 @@ __device__ __forceinline__ float warp_sum32_3(float v) {
     return v + __shfl_xor_sync(0xffffffffu, v, 16);
 }
 
-template <int S, int C, int NT>
+// ONE_RED: the single-reduction form of the same iteration (gato_plan_set_pcg_form).
+template <int S, int C, int NT, bool ONE_RED = false>
 __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveParams2 q) {
     using L = Layout2<S, C>;
     using SL = ScaledLayout<S, C>;
@@ -185,6 +194,64 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
             if (active) st8(half(xw, b, g), wo);                // knot b - 1 sits at slot b
         };
 
+        int iters = p.max_iters;
+        float eta_last = 0.f;
+        if constexpr (ONE_RED) {
+            // Single-reduction PCG (Chronopoulos-Gear): with r~ = P^^-1 r and w = S^ r~ formed first, the two dot
+            // products gamma = r.r~ and delta = r~.w are reduced TOGETHER, and
+            //     beta = gamma / gamma_old,  alpha = gamma / (delta - beta gamma / alpha_old),
+            //     p = r~ + beta p,  s = w + beta s (= S^ p),  lambda += alpha p,  r -= alpha s.
+            // Algebraically the iteration of src/gato_pcg.cuh:300-437 (same gamma_k = r_k^T P^-1 r_k tested against
+            // exit_tol after every update, same 0-based index); one shuffle tree, one partial sum and one division
+            // per iteration instead of two of each.  k = number of updates done.
+            float ss[8], ut[8], u1[8], wv[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ss[j] = 0.f;
+            float* xu = xp;          // r~ travels in the array the two-reduction loop uses for p
+            float gamma_old = 1.f, alpha_old = 1.f;
+            for (int k = 0;; ++k) {
+                if (active) st8(xr_k, rr);
+                __syncthreads();
+                apply(xr, rr, xwr, u1);                       // u1 = (O^ r) own part; w parts -> xwr
+                __syncthreads();
+                ld8(half(xwr, b + 1, g), wv);
+#pragma unroll
+                for (int j = 0; j < HU; ++j) ut[j] = (rr[j] - u1[j]) - wv[j];
+                ut[7] = 0.f;
+                if (active) st8(half(xu, b + 1, g), ut);
+                __syncthreads();
+                apply(xu, ut, xwp, u1);                       // u1 = (O^ r~) own part; w parts -> xwp
+                {
+                    float pg = 0.f, pd = 0.f;
+#pragma unroll
+                    for (int j = 0; j < HU; ++j) {
+                        pg = fmaf(rr[j], ut[j], pg);
+                        pd = fmaf(ut[j], fmaf(2.f, u1[j], ut[j]), pd);
+                    }
+                    pg = warp_sum32_3(pg);
+                    pd = warp_sum32_3(pd);
+                    if (lane == 0) { redA[warp] = pg; redB[warp] = pd; }
+                }
+                __syncthreads();
+                const float gamma = block_partials_sum(redA, NW4), delta = block_partials_sum(redB, NW4);
+                eta_last = gamma;
+                if (k >= 1 && fabsf(gamma) < p.exit_tol) { iters = k - 1; break; }
+                if (k >= p.max_iters) break;
+                const float beta = k == 0 ? 0.f : fast_div(gamma, gamma_old);
+                const float alpha = fast_div(gamma, k == 0 ? delta : fmaf(-beta, fast_div(gamma, alpha_old), delta));
+                ld8(half(xwp, b + 1, g), wv);
+#pragma unroll
+                for (int j = 0; j < HU; ++j) {
+                    const float w = (ut[j] + u1[j]) + wv[j];  // (S^ r~) own part
+                    pp[j] = fmaf(beta, pp[j], ut[j]);
+                    ss[j] = fmaf(beta, ss[j], w);
+                    lam[j] = fmaf(alpha, pp[j], lam[j]);
+                    rr[j] = fmaf(-alpha, ss[j], rr[j]);
+                }
+                gamma_old = gamma;
+                alpha_old = alpha;
+            }
+        } else {
         // r~0 = r - O^ r, eta = r.r~0, p = r~0
         if (active) st8(xr_k, rr);
         __syncthreads();
@@ -205,10 +272,15 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
         if (active) st8(xp_k, pp);
         __syncthreads();
 
-        int iters = p.max_iters;
-        float eta_last = eta;
+        eta_last = eta;
+#ifdef GATO_V5_TRACE
+        const bool trace_on = sys == 0 && tid == 0;
+        long long* trace = reinterpret_cast<long long*>(q.gbuf) + 8;
+#endif
         for (int it = 0; it < p.max_iters; ++it) {
+            V5_STAMP(0);
             apply(xp, pp, xwp, uo);
+            V5_STAMP(1);
             {
                 float part = 0.f;
 #pragma unroll
@@ -216,7 +288,9 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                 part = warp_sum32_3(part);
                 if (lane == 0) redA[warp] = part;
             }
+            V5_STAMP(2);
             __syncthreads();
+            V5_STAMP(3);
             const float v = block_partials_sum(redA, NW4);
             const float alpha = fast_div(eta, v);
             ld8(half(xwp, b + 1, g), wv);
@@ -228,8 +302,11 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
             }
             if (active) st8(xr_k, rr);
             const float eta_seed = rcp_seed(eta);
+            V5_STAMP(4);
             __syncthreads();
+            V5_STAMP(5);
             apply(xr, rr, xwr, uo);
+            V5_STAMP(6);
             {
                 float part = 0.f;
 #pragma unroll
@@ -237,7 +314,9 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                 part = warp_sum32_3(part);
                 if (lane == 0) redB[warp] = part;
             }
+            V5_STAMP(7);
             __syncthreads();
+            V5_STAMP(8);
             const float eta_new = block_partials_sum(redB, NW4);
             eta_last = eta_new;
             if (fabsf(eta_new) < p.exit_tol) { iters = it; break; }
@@ -247,9 +326,12 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
             for (int j = 0; j < HU; ++j) pp[j] = fmaf(beta, pp[j], (rr[j] - uo[j]) - wv[j]);
             if (active) st8(xp_k, pp);
             eta = eta_new;
+            V5_STAMP(9);
             __syncthreads();
+            V5_STAMP(10);
         }
 
+        }
 #include "gato_kernel_v5_dz.inc"
         if (tid == 0) {
             p.iters_out[sys] = iters;

@@ -211,6 +211,11 @@ int gato_plan_set_scaled_chunk(gato_plan* plan, int systems_per_chunk);
  * ~1.6 x faster).  0 = chosen by the size of the whole call (latency below one system per SM), 1 / 2 = forced.  The two
  * agree within the rounding of their summation orders, not bit for bit. */
 int gato_plan_set_scaled_variant(gato_plan* plan, int variant);
+/* Kernel 5, throughput second half: 0 = the update order of src/gato_pcg.cuh:348-421 (two reductions per iteration),
+ * 1 = the single-reduction form of the same iteration (Chronopoulos-Gear: r~ = P^-1 r and w = S r~ first, then
+ * gamma = r.r~ and delta = r~.w reduced together; s = S p by recurrence).  Same exit rule and iteration numbering;
+ * identical in exact arithmetic. */
+int gato_plan_set_pcg_form(gato_plan* plan, int form);
 /* Kernel 5 launches two kernels per chunk; with profiling on, CUDA events are recorded on the launching stream
  * around each of them, and gato_plan_last_profile returns the device time of each half summed over the chunks of the
  * last call (it waits for that call's last event) and the number of kernel launches the call made. */

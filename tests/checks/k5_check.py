@@ -29,8 +29,11 @@ def run(lam, dz, its):
                             exit_tol=b["exit_tol"], max_iters=b["max_iters"], rho=b["rho"], stream=st.cuda_stream)
 
 
-for kernel, chunk in ((2, 0), (5, 0), (5, 148), (5, 1184), (5, 4096), (5, 8192)):
+for kernel, chunk in ((2, 0), (5, 0), (5, 1184), (5, 8192), (51, 0), (51, 1184)):
+    form = 1 if kernel == 51 else 0
+    kernel = 5 if kernel == 51 else kernel
     pl.set_kernel(kernel)
+    pl.set_pcg_form(form)
     if kernel == 5:
         pl.set_scaled_chunk(chunk)
     lam = torch.zeros((n, pl.n_l), device=dev); dz = torch.zeros((n, pl.n_z), device=dev)
@@ -45,7 +48,7 @@ for kernel, chunk in ((2, 0), (5, 0), (5, 148), (5, 1184), (5, 4096), (5, 8192))
         run(lam, dz, its)
     e1.record(); e1.synchronize()
     ms = e0.elapsed_time(e1) / reps
-    key = f"k{kernel}_chunk{chunk}"
+    key = f"k{kernel}{'_onered' if form else ''}_chunk{chunk}"
     out[key] = {"ms_per_batch": ms, "solves_per_s": n / ms * 1e3, "mean_iters": float(its.float().mean())}
     res[key] = (lam.cpu().numpy(), dz.cpu().numpy(), its.cpu().numpy())
     print(key, out[key], flush=True)
@@ -57,8 +60,15 @@ rz = np.linalg.norm(z5 - z2, axis=1) / np.linalg.norm(z2, axis=1)
 out["k5_vs_k2"] = {"max_rel_lambda": float(rl.max()), "mean_rel_lambda": float(rl.mean()), "max_rel_dz": float(rz.max()),
                    "iter_diff_hist": {int(k): int(v) for k, v in zip(*np.unique(i5.astype(int) - i2.astype(int), return_counts=True))},
                    "nan": bool(np.isnan(l5).any())}
-for key in ("k5_chunk148", "k5_chunk8192"):
+for key in ("k5_chunk1184", "k5_chunk8192"):
     out[key]["bitwise_equal_to_default_chunk"] = bool(np.array_equal(res[key][0], l5) and np.array_equal(res[key][2], i5))
+l6, z6, i6 = res["k5_onered_chunk0"]
+rl = np.linalg.norm(l6 - l2, axis=1) / np.linalg.norm(l2, axis=1)
+rz = np.linalg.norm(z6 - z2, axis=1) / np.linalg.norm(z2, axis=1)
+out["k5_onered_vs_k2"] = {"max_rel_lambda": float(rl.max()), "mean_rel_lambda": float(rl.mean()), "max_rel_dz": float(rz.max()),
+                          "iter_diff_hist": {int(k): int(v) for k, v in zip(*np.unique(i6.astype(int) - i2.astype(int), return_counts=True))},
+                          "nan": bool(np.isnan(l6).any())}
+pl.set_pcg_form(0)
 print(json.dumps(out))
 
 # single-solve latency, kernel only (device buffers), kernel 2 vs kernel 5

@@ -516,3 +516,25 @@ print("Test passed")
     r = subprocess.run([sys.executable, "-c", code, bdir, ROOT], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "Test passed" in r.stdout, (r.stdout[-500:], r.stderr[-1500:])
     assert "first run PCG terminated in" in r.stdout and "avg time:" in r.stdout      # the reference's two summary lines
+
+
+def test_kernel5_single_reduction_form():
+    """gato_plan_set_pcg_form(1): the single-reduction (Chronopoulos-Gear) form of the same iteration in the throughput
+    second half of kernel 5.  Same solution within the tolerance, iteration counts within +-1 of the oracle."""
+    n = 600
+    b = iiwa_like_batch_fast(n, 14, 7, 50, seed=2024)
+    pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
+    pl.set_kernel(5)
+    args = (b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    lam0, dz0, it0, _ = pl.solve_batched(*args)
+    pl.set_pcg_form(1)
+    lam1, dz1, it1, _ = pl.solve_batched(*args)
+    assert np.abs(it1.astype(int) - it0.astype(int)).max() <= 1
+    assert max(rel2(lam1[i], lam0[i]) for i in range(n)) < 5e-5
+    for i in range(0, n, 60):
+        lam_o, dz_o, io = oracle(_sys_of(b, i))
+        assert close(lam1[i], lam_o) and close(dz1[i], dz_o) and abs(int(it1[i]) - io["iters"]) <= 1, i
+    for mi in (0, 1, 7):                                     # the loop's edge cases keep the reference's numbering
+        l, _, it, _ = pl.solve_batched(b["G_val"][:300], b["C_val"][:300], b["g"][:300], b["c"][:300], None, b["exit_tol"], mi, 0, b["rho"])
+        assert (it == mi).all() and (mi > 0 or not l.any())
+    pl.close()
