@@ -35,6 +35,13 @@ extern "C" {
 
 typedef struct gato_plan gato_plan; /* opaque: sparsity pattern maps + persistent device workspace */
 
+/* Concurrency.  A plan owns staging buffers, scratch and streams: use it from ONE host thread at a time (the pybind11
+ * module serialises its callers with a mutex; gato_solve_batched_multi gives every device its own plan and thread).
+ * gato_solve_batched_device is asynchronous and may be issued on several streams of one plan from that thread:
+ * kernels 1-3 keep no per-plan device state, kernel 5 keeps one scratch buffer per stream it has seen (at most 8),
+ * kernel 4 (cooperative grid) keeps ONE scratch buffer per plan, so its launches must be on one stream (the chunk
+ * pipeline of gato_solve_batched switches itself off for it). */
+
 /* Which (STATE_SIZE, CONTROL_SIZE) pairs this build of the library carries kernels for.
  * Replaces the compile-time knobs of CMakeLists.txt:18 / install.bash:4-19 at library level; the
  * pybind11 module `gpu_library` still fixes S, C, K at compile time.  Returns the number of pairs;
