@@ -168,8 +168,10 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
         float* xr_k = half(xr, b + 1, g);
         // u = psi_b x_{b-1} (this lane's rows, complete) and the lane pair's w = psi_b^T x_b, of which this lane keeps
         // the half g and stores it into the LEFT knot's slot of xw.  `own` = this lane's entries of x_b.
-        // (Packed FP32 FMAs -- fma.rn.f32x2, pairs along the columns -- were measured here too: 196 FFMA2 instead of
-        // 392 FFMA per iteration, but ~250 MOVs to form and split the pairs; 3.45 vs 3.50 ms per 8192 systems, not kept.)
+        // (Packed FP32 FMAs -- fma.rn.f32x2, pairs along the columns -- were built here twice: 196 FFMA2 instead of
+        // 392 FFMA per iteration, but ptxas adds 210-280 MOVs per iteration to keep their operands in aligned register
+        // pairs at 168 registers, even with the pairs taken straight from 64-bit halves of the 128-bit loads;
+        // 3.45 vs 3.50 ms per 8192 systems the first time, more spills the second.  Not kept.)
         auto apply = [&](float* x, const float (&own)[8], float* xw, float (&u)[8]) {
             float e0[8], e1[8];
             ld8(half(x, b, g), e0);                             // knot b - 1 (slot b), its half g: columns [0, HU) of psi
