@@ -538,3 +538,44 @@ def test_kernel5_single_reduction_form():
         l, _, it, _ = pl.solve_batched(b["G_val"][:300], b["C_val"][:300], b["g"][:300], b["c"][:300], None, b["exit_tol"], mi, 0, b["rho"])
         assert (it == mi).all() and (mi > 0 or not l.any())
     pl.close()
+
+
+def test_kernel5_block_input_and_dropin_batch():
+    """Kernel 5 behind the other entry points: the block-input plan (dense per-knot layouts, no CSR) and the drop-in
+    module's linsys_solve_batched (which selects it on its own for a device-filling batch)."""
+    import subprocess
+    import refrun
+    from test_gpu_parity import _dense_layouts
+    n = 330
+    b = iiwa_like_batch_fast(n, 14, 7, 50, seed=555)
+    lay = [_dense_layouts(_sys_of(b, i)) for i in range(n)]
+    Gd = np.stack([x[0] for x in lay]); Cd = np.stack([x[1] for x in lay])
+    pb = Plan.from_blocks(14, 7, 50, max_batch=n)
+    assert pb.kernel_for(n) == 5
+    lam, dz, it, _ = pb.solve_batched(Gd, Cd, b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    for i in (0, 100, n - 1):
+        lam_o, dz_o, io = oracle(_sys_of(b, i))
+        assert close(lam[i], lam_o) and close(dz[i], dz_o) and abs(int(it[i]) - io["iters"]) <= 1, i
+    pb.close()
+    d = refrun.dropin_module_dir(14, 7, 50)
+    if d is None:
+        pytest.skip("drop-in module not built")
+    code = r"""
+import sys, numpy as np, os
+os.environ["GATO_B200_QUIET"] = "1"
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[2])
+import gpu_library
+from gato_python_b200.problems import iiwa_like_batch_fast
+b = iiwa_like_batch_fast(330, 14, 7, 50, seed=555)
+lam, dz, it = gpu_library.linsys_solve_batched(b["G_row"], b["G_col"], b["G_val"], b["C_row"], b["C_col"], b["C_val"], b["g"], b["c"],
+                                               float(b["exit_tol"]), int(b["max_iters"]), float(b["rho"]))
+np.savez(sys.argv[3], lam=lam, dz=dz, it=it)
+"""
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "o.npz")
+        r = subprocess.run([sys.executable, "-c", code, d, ROOT, out], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-1500:]
+        o = np.load(out)
+    assert np.abs(o["it"].astype(int) - it.astype(int)).max() <= 1
+    assert max(rel2(o["lam"][i], lam[i]) for i in range(n)) < 1e-5      # CSR path vs block path of the same kernel
