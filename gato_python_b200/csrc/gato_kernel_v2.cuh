@@ -132,13 +132,17 @@ struct MapControl {
     __device__ static constexpr int row(int lik_, int i) { return lik_ * N + i < C ? lik_ * N + i : -1; }
 };
 
+// Sum over the warp in THREE dependent shuffle steps instead of five (4-ary, 4-ary, 2-ary: seven shuffles): the PCG
+// loops wait on the dependent chain of their reductions, not on shuffle issue slots.  Every lane ends with the same
+// bits (each level adds the same pair sums, and a + b == b + a exactly).
 __device__ __forceinline__ float warp_sum32(float v) {
-    v += __shfl_xor_sync(0xffffffffu, v, 16);
-    v += __shfl_xor_sync(0xffffffffu, v, 8);
-    v += __shfl_xor_sync(0xffffffffu, v, 4);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    return v;
+    const float a1 = __shfl_xor_sync(0xffffffffu, v, 1), a2 = __shfl_xor_sync(0xffffffffu, v, 2),
+                a3 = __shfl_xor_sync(0xffffffffu, v, 3);
+    v = (v + a1) + (a2 + a3);
+    const float b1 = __shfl_xor_sync(0xffffffffu, v, 4), b2 = __shfl_xor_sync(0xffffffffu, v, 8),
+                b3 = __shfl_xor_sync(0xffffffffu, v, 12);
+    v = (v + b1) + (b2 + b3);
+    return v + __shfl_xor_sync(0xffffffffu, v, 16);
 }
 
 // fixed-order sum of the per-warp partials (16-byte broadcast loads; same bits in every thread)

@@ -40,19 +40,6 @@
 
 namespace gato {
 
-// Sum over the warp in THREE dependent shuffle steps instead of five (4-ary, 4-ary, 2-ary: seven shuffles): this kernel
-// waits on the dependent chain of the reduction, not on shuffle issue slots.  Every lane ends with the same bits
-// (each level adds the same pair sums, and a + b == b + a exactly).
-__device__ __forceinline__ float warp_sum32_3(float v) {
-    const float a1 = __shfl_xor_sync(0xffffffffu, v, 1), a2 = __shfl_xor_sync(0xffffffffu, v, 2),
-                a3 = __shfl_xor_sync(0xffffffffu, v, 3);
-    v = (v + a1) + (a2 + a3);
-    const float b1 = __shfl_xor_sync(0xffffffffu, v, 4), b2 = __shfl_xor_sync(0xffffffffu, v, 8),
-                b3 = __shfl_xor_sync(0xffffffffu, v, 12);
-    v = (v + b1) + (b2 + b3);
-    return v + __shfl_xor_sync(0xffffffffu, v, 16);
-}
-
 // ONE_RED: the single-reduction form of the same iteration (gato_plan_set_pcg_form).
 template <int S, int C, int NT, bool ONE_RED = false>
 __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveParams2 q) {
@@ -230,8 +217,8 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                         pg = fmaf(rr[j], ut[j], pg);
                         pd = fmaf(ut[j], fmaf(2.f, u1[j], ut[j]), pd);
                     }
-                    pg = warp_sum32_3(pg);
-                    pd = warp_sum32_3(pd);
+                    pg = warp_sum32(pg);
+                    pd = warp_sum32(pd);
                     if (lane == 0) { redA[warp] = pg; redB[warp] = pd; }
                 }
                 __syncthreads();
@@ -263,7 +250,7 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
             float part = 0.f;
 #pragma unroll
             for (int j = 0; j < HU; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
-            part = warp_sum32_3(part);
+            part = warp_sum32(part);
             if (lane == 0) redB[warp] = part;
         }
         __syncthreads();
@@ -287,7 +274,7 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                 float part = 0.f;
 #pragma unroll
                 for (int j = 0; j < HU; ++j) part = fmaf(pp[j], fmaf(2.f, uo[j], pp[j]), part);
-                part = warp_sum32_3(part);
+                part = warp_sum32(part);
                 if (lane == 0) redA[warp] = part;
             }
             V5_STAMP(2);
@@ -313,7 +300,7 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
                 float part = 0.f;
 #pragma unroll
                 for (int j = 0; j < HU; ++j) part = fmaf(rr[j], fmaf(-2.f, uo[j], rr[j]), part);
-                part = warp_sum32_3(part);
+                part = warp_sum32(part);
                 if (lane == 0) redB[warp] = part;
             }
             V5_STAMP(7);
