@@ -17,6 +17,7 @@
 #include "gato_kernel_v2.cuh"
 #include "gato_kernel_v5.cuh"
 #include "gato_kernel_v5_lat.cuh"
+#include "gato_kernel_v5_gamma.cuh"
 
 #ifndef GATO_EXTRA_S
 #define GATO_EXTRA_S 0
@@ -113,6 +114,7 @@ struct gato_plan {
     cudaStream_t scr_stream[kScr] = {};
     int nscr = 0;
     int v5_chunk = 0;       // kernel 5: systems per chunk (0 = automatic)
+    int v5_shared = 0;      // kernel 5, calls with one matrix pair for every system (ldG == ldC == 0): 0 = first half once, 1 = per system
     int v5_variant = 0;     // kernel 5, second half: 0 = by call size, 1 = latency kernel (4 lanes per knot), 2 = throughput kernel
     int profile = 0;        // kernel 5: record CUDA events around each of its launches (gato_plan_set_profiling)
     std::vector<cudaEvent_t> prof_ev;   // 3 per chunk of the last profiled call: before first half | between | after second
@@ -384,6 +386,8 @@ int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st
     return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
 }
 
+constexpr int kV5SharedChunk = 1 << 16;   // systems per gamma^ array of the shared-matrix path (3.2 KB each at IIWA-50)
+
 // first_only: run just the first half on the first system and leave its scratch in pl->dscr (parity hook)
 template <int S, int C>
 int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool first_only) {
@@ -408,12 +412,15 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
     q.gbuf = q.scr + (size_t)chunk * (size_t)per;     // behind the scratch: the second half's work counter
     q.scr_ld = per;
     const gato::SolveParams base = q.p;
-    const int nchunk = (base.nsys + chunk - 1) / chunk;
     // which second half: decided by the size of the whole call (every chunk of it runs the same kernel, so the result
     // does not depend on the chunking); gato_plan_set_scaled_variant overrides
     const int whole = pl->batch_hint > 0 ? pl->batch_hint : base.nsys;
     const bool lat = 4 * pl->K <= 224 && (pl->v5_variant == 1 || (pl->v5_variant == 0 && whole < sms));
     const bool prof = pl->profile && !first_only;
+    // One matrix pair for the whole call (ldG == ldC == 0): theta, phi, M and psi are computed ONCE; a small kernel
+    // forms gamma^ of every system and the second half reads the one scratch.  (Throughput variant only.)
+    const bool shared = !first_only && !lat && pl->v5_shared != 1 && base.nsys > 1 && base.ldG == 0 && base.ldC == 0;
+    const int nchunk = shared ? (base.nsys + kV5SharedChunk - 1) / kV5SharedChunk : (base.nsys + chunk - 1) / chunk;
     if (prof) {
         while ((int)pl->prof_ev.size() < 3 * nchunk) {
             cudaEvent_t e;
@@ -421,6 +428,43 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
             pl->prof_ev.push_back(e);
         }
         pl->prof_chunks = 0;
+    }
+    if (shared) {
+        if constexpr (HasV5<S>::value) {
+            using SL = gato::ScaledLayout<S, C>;
+            using L = gato::Layout2<S, C>;
+            const int cmax = base.nsys < kV5SharedChunk ? base.nsys : kV5SharedChunk;
+            const size_t o_shx = (size_t)per * sizeof(float) + 4096;          // scratch of ONE system | counter | phi, M64 | gamma^
+            const size_t o_gam = o_shx + (((size_t)pl->K * SL::KSHX * sizeof(float) + 255) & ~(size_t)255);
+            const long long gam_ld = (long long)pl->K * L::VS;
+            GATO_CUDA(pl->dscr[si].ensure(o_gam + (size_t)cmax * (size_t)gam_ld * sizeof(float)));
+            char* b0 = (char*)pl->dscr[si].p;
+            q.scr = (float*)b0;
+            q.gbuf = q.scr + (size_t)per;
+            q.scr_ld = 0;
+            q.shx = (float*)(b0 + o_shx);
+            q.p = slice_params(base, 0, 1);
+            if (prof) GATO_CUDA(cudaEventRecord(pl->prof_ev[0], st));
+            int rc = launch_v5_first<S, C>(pl, q, st);
+            if (rc) return rc;
+            q.gam = (float*)(b0 + o_gam);
+            q.gam_ld = gam_ld;
+            const int gnt = 32 * L::warps(pl->K);
+            for (int r0 = 0, ci = 0; r0 < base.nsys; r0 += kV5SharedChunk, ++ci) {
+                const int nr = base.nsys - r0 < kV5SharedChunk ? base.nsys - r0 : kV5SharedChunk;
+                q.p = slice_params(base, r0, nr);
+                if (prof && ci > 0) GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci], st));
+                if (ci > 0) GATO_CUDA(cudaMemsetAsync(q.gbuf, 0, sizeof(int), st));   // the work counter (the first half reset it for chunk 0)
+                const unsigned ggrid = (unsigned)(nr < 8 * sms ? nr : 8 * sms);
+                gato::gato_gamma_scaled<S, C><<<ggrid, gnt, 0, st>>>(q);
+                GATO_CUDA(cudaGetLastError());
+                if (prof) GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci + 1], st));
+                if ((rc = launch_v5_second<S, C>(pl, q, st, false))) return rc;
+                if (prof) { GATO_CUDA(cudaEventRecord(pl->prof_ev[3 * ci + 2], st)); pl->prof_chunks = ci + 1; }
+            }
+            pl->prof_launches = 1 + 2 * nchunk;
+            return GATO_OK;
+        }
     }
     for (int r0 = 0, ci = 0; r0 < base.nsys; r0 += chunk, ++ci) {
         const int nr = base.nsys - r0 < chunk ? base.nsys - r0 : chunk;
@@ -756,7 +800,7 @@ bool v2_stages(const gato_plan* pl) {
 }
 
 int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
-    gato::SolveParams2 q;
+    gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
@@ -778,7 +822,7 @@ int launch_solve_v5(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st, 
 }
 
 int launch_solve_v2cl(const gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
-    gato::SolveParams2 q;
+    gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
@@ -797,7 +841,7 @@ void v2_maps_for(const gato_plan* pl, const std::vector<int>& gmap, const std::v
 }
 
 int launch_solve_v2grid(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
-    gato::SolveParams2 q;
+    gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;

@@ -106,6 +106,8 @@ struct ScaledLayout {
     static constexpr int oM = oPSI + 2 * PSIL;
     static constexpr int oGAM = oM + S * L::VS;
     static constexpr int KSCR = oGAM + L::VS;
+    // shared-matrix extras per knot: phi_b as in shared memory ([c][VS], rows in pos layout) | M_b in FP64 [S][S]
+    static constexpr int xPHI = 0, xM64 = S * L::VS, KSHX = xM64 + 2 * S * S;
     // FP64 scratch inside a knot's (dead) shared-memory region: M64 [S][S] doubles, then T64 [S][2 HT] doubles
     static constexpr int HT = (L::HALFU + 1) & ~1;
     static constexpr int oM64 = 0, oT64 = 2 * S * S;
@@ -215,6 +217,13 @@ struct SolveParams2 {
     float* gbuf;          // grid variant: global scratch, [2][256] per-CTA dot partials | [ncta][3][2][VS] boundary slices
     float* scr;           // kernel 5 (scaled system): per-system scratch between its two kernels (ScaledLayout)
     long long scr_ld;     // floats between consecutive systems in scr
+    // kernel 5 with matrices shared by all systems of a call (ldG == ldC == 0): the first half runs ONCE and also leaves
+    // phi_b and M_b (FP64) per knot in shx (ScaledLayout::KSHX floats per knot); gato_gamma_scaled then forms gamma^ of
+    // every system into gam, and the second half reads psi / M / the regions from the one scratch (scr_ld = 0), gamma^
+    // from gam and q, r from the caller's g.
+    float* shx;
+    float* gam;           // [nsys][K VS] gamma^ in pos layout, or null: gamma^ sits in the scratch
+    long long gam_ld;
 };
 
 // ---- TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier) ---------------------

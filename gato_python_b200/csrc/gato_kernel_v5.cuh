@@ -139,8 +139,10 @@ __global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveP
         {
             float t[8];
             if (active) {
-                const float4 t0 = __ldcg(reinterpret_cast<const float4*>(kg + SL::oGAM + g * HALFP));
-                const float4 t1 = __ldcg(reinterpret_cast<const float4*>(kg + SL::oGAM + g * HALFP) + 1);
+                // gamma^: from the scratch, or (matrices shared by the call) from the per-system array gato_gamma_scaled filled
+                const float* gsrc = (q.gam != nullptr ? q.gam + (long long)sys * q.gam_ld + b * VS : kg + SL::oGAM) + g * HALFP;
+                const float4 t0 = __ldcg(reinterpret_cast<const float4*>(gsrc));
+                const float4 t1 = __ldcg(reinterpret_cast<const float4*>(gsrc) + 1);
                 t[0] = t0.x; t[1] = t0.y; t[2] = t0.z; t[3] = t0.w; t[4] = t1.x; t[5] = t1.y; t[6] = t1.z; t[7] = t1.w;
             } else {
 #pragma unroll

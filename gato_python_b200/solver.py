@@ -26,7 +26,7 @@ SYMBOLS = [
     "gato_plan_set_preconditioner", "gato_plan_get_preconditioner",
     "gato_scaled_layout", "gato_scaled_debug", "gato_plan_set_scaled_chunk", "gato_plan_get_kernel_for",
     "gato_plan_set_profiling", "gato_plan_last_profile", "gato_solve_batched_multi",
-    "gato_plan_set_scaled_variant", "gato_plan_set_pcg_form",
+    "gato_plan_set_scaled_variant", "gato_plan_set_pcg_form", "gato_plan_set_shared_matrix_path",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -76,6 +76,7 @@ def lib():
                                            _fp, _ll, _fp, _fp, _ip, C.c_float, C.c_int, C.c_int, C.c_float, _fp]
     L.gato_plan_set_scaled_variant.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_pcg_form.argtypes = [C.c_void_p, C.c_int]
+    L.gato_plan_set_shared_matrix_path.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_profiling.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_last_profile.argtypes = [C.c_void_p, _fp, _fp, _ip]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
@@ -304,6 +305,11 @@ class Plan:
     def set_scaled_variant(self, variant):
         """Kernel 5, second half: 0 = by call size, 1 = latency kernel (4 lanes per knot), 2 = throughput kernel."""
         _check(lib().gato_plan_set_scaled_variant(self._h, int(variant)))
+
+    def set_shared_matrix_path(self, on):
+        """Kernel 5, batched calls with ONE matrix pair (ldG == ldC == 0): True (default) = Schur phase and factorisation
+        once per call, False = per system."""
+        _check(lib().gato_plan_set_shared_matrix_path(self._h, int(bool(on))))
 
     def set_pcg_form(self, form):
         """Kernel 5, throughput second half: 0 = two reductions per iteration (reference order), 1 = single reduction."""

@@ -218,6 +218,12 @@ int gato_plan_set_scaled_chunk(gato_plan* plan, int systems_per_chunk);
  * ~1.6 x faster).  0 = chosen by the size of the whole call (latency below one system per SM), 1 / 2 = forced.  The two
  * agree within the rounding of their summation orders, not bit for bit. */
 int gato_plan_set_scaled_variant(gato_plan* plan, int variant);
+/* Kernel 5, batched calls whose systems share ONE matrix pair (ldG == 0 and ldC == 0: the reference's G / C with many
+ * right-hand sides g, c -- sampling, rollouts): theta, phi, the factor M and psi then belong to the call, so the first
+ * half (src/gato_schur.cuh:26-496 plus the congruence) runs once, gato_gamma_scaled forms gamma^ = M gamma of every
+ * system, and the second half reads the one scratch.  on = 1 (default) takes that path with the throughput second
+ * half; on = 0 recomputes everything per system (the path the parity tests compare it with). */
+int gato_plan_set_shared_matrix_path(gato_plan* plan, int on);
 /* Kernel 5, throughput second half: 0 = the update order of src/gato_pcg.cuh:348-421 (two reductions per iteration),
  * 1 = the single-reduction form of the same iteration (Chronopoulos-Gear: r~ = P^-1 r and w = S r~ first, then
  * gamma = r.r~ and delta = r~.w reduced together; s = S p by recurrence).  Same exit rule and iteration numbering;

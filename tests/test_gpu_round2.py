@@ -385,6 +385,49 @@ def test_kernel5_batch_matches_single_and_oracle():
     pl.close()
 
 
+@pytest.mark.parametrize("name,K", [("diag", 50), ("dense", 50), ("diag", 33), ("diag", 2)])
+def test_kernel5_shared_matrix_path(name, K):
+    """One matrix pair, many right-hand sides (ldG == ldC == 0): the first half runs once, gato_gamma_scaled forms
+    gamma^ of every system, the second half reads the one scratch.  Compared with the per-system path of the same
+    kernel (same arithmetic: bit for bit), with fresh single solves and with the oracle."""
+    n = 640
+    prob = iiwa_like(K=K, seed=11, dense_G=(name == "dense"), dense_AB=(name == "dense"))
+    rng = np.random.default_rng(12)
+    g = (prob["g"][None, :] * (1.0 + 0.5 * rng.standard_normal((n, prob["g"].size)))).astype(np.float32)
+    c = (prob["c"][None, :] + 0.1 * rng.standard_normal((n, prob["c"].size))).astype(np.float32)
+    pl = Plan(14, 7, K, prob["G_row"], prob["G_col"], prob["C_row"], prob["C_col"], max_batch=n)
+    pl.set_kernel(5)
+    pl.set_scaled_variant(2)
+    args = (prob["G_val"], prob["C_val"], g, c, None, prob["exit_tol"], prob["max_iters"], 0, prob["rho"])
+    lam, dz, it, _ = pl.solve_batched(*args)
+    pl.set_profiling(True)
+    lam_b, dz_b, it_b, _ = pl.solve_batched(*args)
+    assert pl.last_profile()[2] == 3                      # first half (one system), gamma kernel, second half
+    pl.set_profiling(False)
+    assert np.array_equal(lam, lam_b) and np.array_equal(dz, dz_b)
+    pl.set_shared_matrix_path(False)
+    lam2, dz2, it2, _ = pl.solve_batched(*args)
+    pl.set_profiling(True)
+    pl.solve_batched(*args)
+    assert pl.last_profile()[2] == 2
+    pl.set_profiling(False)
+    assert np.array_equal(it, it2)
+    assert np.array_equal(lam, lam2) and np.array_equal(dz, dz2)
+    for i in range(0, n, 64):
+        sysi = dict(prob, g=g[i], c=c[i])
+        lam_o, dz_o, io = oracle(sysi)
+        if K > 1:
+            assert close(lam[i], lam_o) and close(dz[i], dz_o), (i, rel2(lam[i], lam_o), rel2(dz[i], dz_o))
+        assert abs(int(it[i]) - io["iters"]) <= 1
+    # per-system matrices that happen to be equal: the general path, same bits
+    pl.set_shared_matrix_path(True)
+    Gb = np.broadcast_to(prob["G_val"], (n, prob["G_val"].size)).copy()
+    Cb = np.broadcast_to(prob["C_val"], (n, prob["C_val"].size)).copy()
+    lam3, dz3, it3, _ = pl.solve_batched(Gb, Cb, g, c, None, prob["exit_tol"], prob["max_iters"], 0, prob["rho"])
+    assert np.array_equal(lam, lam3) and np.array_equal(dz, dz3) and np.array_equal(it, it3)
+    pl.close()
+
+
 # ---- boundary hardening -------------------------------------------------------------------------------------------
 def test_multiplan_single_process_gather_vs_oracle():
     """gato_solve_batched_multi: one process, one host thread per device, results gathered into one host buffer.  With a
