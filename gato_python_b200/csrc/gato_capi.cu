@@ -104,6 +104,8 @@ struct gato_plan {
     // device: pattern maps
     int *d_gmap = nullptr, *d_cmap = nullptr, *d_gstart = nullptr, *d_cstart = nullptr;
     int *d_gdst2 = nullptr, *d_cdst2 = nullptr;   // v2: absolute shared-memory destinations
+    int* d_cperm = nullptr;                       // v2, one CTA: (C_val index, destination) pairs in bank-sorted order
+    int ncperm = 0;
     // device: staged inputs / outputs for the host-buffer entry points
     DevBuf dG, dC, dg, dc, dl, dlo, ddz, dit, dbg;
     DevBuf dgrid;           // kernel 4: global scratch of the cooperative-grid variant
@@ -256,7 +258,11 @@ int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
         std::lock_guard<std::mutex> lk(mu);
         const int di = pl->device % kMaxDev;
         if (!raised[di]) {
+#ifdef GATO_S_TRACE
+            GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_optin - 256));   // trace sums are static shared memory
+#else
             GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_optin));
+#endif
             raised[di] = true;
         }
     }
@@ -646,6 +652,36 @@ void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::
     }
 }
 
+// The scatter of C's non-zeros into the knot regions, reordered so that every 32 consecutive entries (one warp store)
+// fall into 32 distinct shared-memory banks -- and come from 32 distinct banks of the staged copy of C_val.  CSR order
+// puts the entries of one row of [A | B] next to each other, and those sit VS = 16 words apart: 16 of 32 lanes on one
+// bank (measured 21.1 M shared-memory wavefronts per launch where 2.2 M are needed).  Greedy edge colouring of the
+// bipartite (source bank, destination bank) multigraph: each entry goes to the first warp store that has both banks
+// free; the unused lanes of a store carry destination -1.  -> interleaved (source, destination) pairs.
+std::vector<int> v2_bank_sorted_scatter(const std::vector<int>& cdst) {
+    struct Grp { unsigned src = 0, dst = 0; int n = 0; int e[32]; };
+    std::vector<Grp> grp;
+    size_t first_open = 0;
+    for (size_t t = 0; t < cdst.size(); ++t) {
+        if (cdst[t] < 0) continue;
+        const unsigned bs = 1u << (t & 31), bd = 1u << (cdst[t] & 31);
+        size_t g = first_open;
+        while (g < grp.size() && ((grp[g].src & bs) || (grp[g].dst & bd))) ++g;
+        if (g == grp.size()) grp.emplace_back();
+        grp[g].src |= bs; grp[g].dst |= bd;
+        grp[g].e[grp[g].n++] = (int)t;
+        while (first_open < grp.size() && grp[first_open].n == 32) ++first_open;
+    }
+    std::vector<int> out;
+    out.reserve(grp.size() * 64);
+    for (const Grp& g : grp)
+        for (int i = 0; i < 32; ++i) {
+            out.push_back(i < g.n ? g.e[i] : 0);
+            out.push_back(i < g.n ? cdst[g.e[i]] : -1);
+        }
+    return out;
+}
+
 // -DGATO_EXTRA_S/-DGATO_EXTRA_C add one more (STATE_SIZE, CONTROL_SIZE) pair to every kernel family
 #if defined(GATO_ONLY_IIWA)   // development builds: the (14, 7) kernels only (a fifth of the compile time)
 #define GATO_FOR_SIZES(X) X(14, 7)
@@ -803,6 +839,7 @@ int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v2_sc<s, c>(pl, q, st);
     GATO_FOR_SIZES(X)
@@ -814,6 +851,7 @@ int launch_solve_v5(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st, 
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v5_sc<s, c>(pl, q, st, first_only);
     GATO_FOR_SIZES(X)
@@ -825,6 +863,7 @@ int launch_solve_v2cl(const gato_plan* pl, const gato::SolveParams& p, cudaStrea
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v2cl_sc<s, c>(pl, q, st);
     GATO_FOR_SIZES(X)
@@ -844,6 +883,7 @@ int launch_solve_v2grid(gato_plan* pl, const gato::SolveParams& p, cudaStream_t 
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v2grid_sc<s, c>(pl, q, st);
     GATO_FOR_SIZES(X)

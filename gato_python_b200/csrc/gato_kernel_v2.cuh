@@ -221,6 +221,11 @@ struct SolveParams2 {
     // phi_b and M_b (FP64) per knot in shx (ScaledLayout::KSHX floats per knot); gato_gamma_scaled then forms gamma^ of
     // every system into gam, and the second half reads psi / M / the regions from the one scratch (scr_ld = 0), gamma^
     // from gam and q, r from the caller's g.
+    // one-CTA kernels with staged values: the non-zeros of C in an order whose every 32 consecutive entries hit 32
+    // distinct banks on both sides of the scatter -- (index into C_val, shared-memory destination) pairs, destination -1 =
+    // padding; null: scatter in CSR order through cdst
+    const int2* cperm;
+    int ncperm;
     float* shx;
     float* gam;           // [nsys][K VS] gamma^ in pos layout, or null: gamma^ sits in the scratch
     long long gam_ld;
@@ -310,6 +315,19 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // the PCG loop -- the congruence  S^ = M S M^T  with M_b = inverse Cholesky factor of theta_b, formed in FP64, whose
 // diagonal blocks are the identity: only psi_b = M_b phi_b M_{b-1}^T, gamma^ = M gamma and M leave the SM (to the
 // per-system scratch q.scr), together with a verbatim copy of the knot regions for the dz phase of the second half.
+// Development builds (-DGATO_S_TRACE): thread 0 of CTA 0 accumulates clock64() differences between the phase boundaries
+// of every system it takes (static shared memory) and leaves the sums 2 KB behind the work counter of kernel 5.
+// 1: fetch the first round of the bank-sorted scatter map before shared memory is cleared (measured: the 48 live
+// registers spill, 1.38 vs 1.32 ms per 8192 systems -- off)
+#ifndef GATO_PERM_PREFETCH
+#define GATO_PERM_PREFETCH 0
+#endif
+#ifdef GATO_S_TRACE
+#define S_STAMP(i) do { if (SCALED && blockIdx.x == 0 && threadIdx.x == 0) { const long long t_ = clock64(); s_tr[1 + (i)] += t_ - s_tr[0]; s_tr[0] = t_; } } while (0)
+#else
+#define S_STAMP(i) do { } while (0)
+#endif
+
 template <int S, int C, int NT, bool CL = false, bool GRID = false, bool SCALED = false>
 __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 q) {
     static_assert(!GRID || CL, "the grid variant uses the cluster variant's decomposition");
@@ -377,6 +395,10 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
     __syncthreads();
 
     // persistent: CTA i solves systems i, i + gridDim.x, ...
+#ifdef GATO_S_TRACE
+    __shared__ long long s_tr[24];
+    if (threadIdx.x == 0) { for (int i = 0; i < 24; ++i) s_tr[i] = 0; s_tr[0] = clock64(); }
+#endif
 #pragma unroll 1
     while (true) {
         int sys = ctl[0];
@@ -579,7 +601,20 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         };
 
 
-        stamp(p, 0);
+        // The scatter map of C in bank-sorted order (one-CTA kernels, staged values): its first round is fetched now and
+        // arrives while shared memory is cleared.
+        constexpr int UP = 24;
+        const bool permuted = !CL && staged && q.cperm != nullptr;
+        int2 pe[UP];
+        auto load_perm = [&](int t0) {
+#pragma unroll
+            for (int u = 0; u < UP; ++u) {
+                const int t = t0 + u * NT;
+                pe[u] = t < q.ncperm ? __ldg(q.cperm + t) : make_int2(0, -1);
+            }
+        };
+        if (GATO_PERM_PREFETCH && permuted) load_perm(tid);
+        stamp(p, 0); S_STAMP(0);
         {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0.
             // A persistent CTA's later systems with a purely diagonal G write exactly the words its first system
             // wrote in the knot regions (same pattern, reciprocals in place): only the iterates need clearing.
@@ -589,7 +624,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         sync_all();   // cluster variant: no CTA pushes into a halo slot that its owner has yet to clear
-        stamp(p, 1);
+        stamp(p, 1); S_STAMP(1);
 
         const float* cv = p.c + (long long)sys * p.ldc;
         // value sources: the staging area once this system's bulk copies have landed, else global memory
@@ -605,6 +640,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             gv = stg + stage_span(gv, (S + C) * K - C).lead;
             mbar_wait(mbar, (uint32_t)ctl[1]);
         }
+        S_STAMP(10);
 
         // ==== 1. unpack: coalesced reads of the CSR values, scatter into the dense per-knot blocks ====
         // One CTA per SM means memory latency is hidden only by the loads each thread keeps in flight:
@@ -618,6 +654,21 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             const int zA = CL ? kA * (S + C) : 0, zB = CL ? min(kB * (S + C), (S + C) * K - C) : (S + C) * K - C;
             const int shift = CL ? (k0 - 1) * KN : 0;
             constexpr int UB = 16;
+            if (permuted) {
+                // the staged copy of C_val through a pointer the compiler knows to be shared memory: a generic load of 32
+                // scattered words is split per 128-byte line before it reaches the banks (measured: 2.3 x the whole phase)
+                const float* CvS = smem + q.stage_off + stage_span(p.C_val + (long long)sys * p.ldC, q.nnzC).lead;
+#pragma unroll 1
+                for (int t0 = tid; t0 < q.ncperm; t0 += NT * UP) {
+                    if (!GATO_PERM_PREFETCH || t0 != tid) load_perm(t0);
+                    float v[UP];
+#pragma unroll
+                    for (int u = 0; u < UP; ++u) v[u] = pe[u].y >= 0 ? CvS[pe[u].x] : 0.f;
+#pragma unroll
+                    for (int u = 0; u < UP; ++u)
+                        if (pe[u].y >= 0) smem[pe[u].y] = v[u];
+                }
+            } else
 #pragma unroll 1
             for (int t0 = cA + tid; t0 < cB; t0 += NT * UB) {
                 int m[UB];
@@ -664,7 +715,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             issue_stage(sys + (int)gridDim.x);
         }
-        stamp(p, 2);
+        stamp(p, 2); S_STAMP(2);
 
         // ---- Schur-phase helpers (own-row mapping) -----------------------------------------------------
         // row `row` of a row-major [.][VS] matrix in pos layout -> registers indexed by true column
@@ -768,7 +819,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                         }
                     }
                     __syncthreads();
-                    stamp(p, 3);
+                    stamp(p, 3); S_STAMP(3);
                     continue;
                 }
                 if (inv) {
@@ -900,7 +951,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                     }
                 }
                 __syncthreads();   // every stage's A, B, Q^-1, R^-1, q, r are in shared memory
-                stamp(p, 3);
+                stamp(p, 3); S_STAMP(3);
             }
         }
         // a = theta_b^-1 rows; block row 0 uses raw Q0 instead (the reference's Pinv[0] = Q0)
@@ -909,7 +960,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             for (int i = 0; i < OWN; ++i)
                 if (ovr[i]) load_row(kn + L::oPhi + orow[i] * VS, a[i]);
         }
-        stamp(p, 4);
+        stamp(p, 4); S_STAMP(4);
         __syncthreads();   // phi_b of every block row is in shared memory
 
         if constexpr (SCALED) {
@@ -1388,7 +1439,12 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             ctl[1] ^= 1;
         }
         __syncthreads();
+        S_STAMP(11);
     }
+#ifdef GATO_S_TRACE
+    if (SCALED && blockIdx.x == 0 && threadIdx.x == 0)
+        for (int i = 0; i < 24; ++i) (reinterpret_cast<long long*>(q.gbuf) + 256)[i] = s_tr[i];
+#endif
 }
 
 }  // namespace gato
