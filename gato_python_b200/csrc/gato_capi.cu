@@ -903,3 +903,99 @@ int launch_auto(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st) {
 }  // namespace
 
 #include "gato_capi_entry.inc"
+
+// ---- kernel 5 without any allocation: its scratch in a file-scope device array ----------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops).  Everything else in this library sizes its scratch with cudaMalloc on first
+// use (pl->dscr); this entry point uses ONE fixed array that every GPU which loads the library holds until exit.  All
+// calls share it and it keeps the last call's contents: calls that overlap on the GPU (two streams, two plans, two host
+// threads) race on it.
+namespace {
+constexpr long long kNoAllocFloats = 2ll << 20;          // 8 MiB
+constexpr long long kNoAllocTail = 1024;                 // floats behind the systems' scratch: the second half's work counter
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in for the symbol, not a device address: the address a kernel can
+// use comes from cudaGetSymbolAddress, once per device, with that device current.
+int noalloc_scratch_ptr(int device, float** out) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static float* ptr[kMaxDev];
+    if (device < 0 || device >= kMaxDev) return fail(GATO_EINVAL, "device %d: the no-allocation path serves devices 0..%d", device, kMaxDev - 1);
+    std::lock_guard<std::mutex> lk(mu);
+    if (ptr[device] == nullptr) {
+        int cur = -1;
+        GATO_CUDA(cudaGetDevice(&cur));
+        if (cur != device) return fail(GATO_EINVAL, "device %d is not current (current: %d)", device, cur);
+        float* p = nullptr;
+        GATO_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (p == nullptr) return fail((int)cudaErrorInvalidSymbol, "cudaGetSymbolAddress returned a null address");
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return GATO_OK;
+}
+
+template <int S, int C>
+int launch_v5_noalloc_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
+    if (!v5_ok_sc<S, C>(pl)) return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
+    const long long per = v5_scratch_per_system<S, C>(pl);
+    const long long cap = (kNoAllocFloats - kNoAllocTail) / per;
+    if (q.p.nsys > cap)
+        return fail(GATO_EINVAL, "nsys=%d: the fixed scratch (%lld bytes) holds at most %lld systems of K=%d (%lld bytes each)",
+                    q.p.nsys, kNoAllocFloats * 4, cap, pl->K, per * 4);
+    float* scr = nullptr;
+    int rc = noalloc_scratch_ptr(pl->device, &scr);
+    if (rc) return rc;
+    q.scr = scr;
+    q.gbuf = scr + (kNoAllocFloats - kNoAllocTail);
+    q.scr_ld = per;
+    // what must start at zero: the second half's work counter (the first half also resets it; the array keeps the last
+    // call's contents).  Every scratch word the second half reads is written by the first half of the same call.
+    GATO_CUDA(cudaMemsetAsync(q.gbuf, 0, 256, st));
+    const int sms = pl->sm_count > 0 ? pl->sm_count : 148;
+    const bool lat = 4 * pl->K <= 224 && (pl->v5_variant == 1 || (pl->v5_variant == 0 && q.p.nsys < sms));   // as launch_v5_sc decides
+    if ((rc = launch_v5_first<S, C>(pl, q, st))) return rc;
+    return launch_v5_second<S, C>(pl, q, st, lat);
+}
+}  // namespace
+
+extern "C" {
+
+int gato_noalloc_max_systems(const gato_plan* pl) {
+    if (!pl) return fail(GATO_EINVAL, "plan is NULL");
+    if (!v5_ok(pl)) return 0;
+    const long long per = v5_scratch_floats(pl);
+    return per > 0 ? (int)((kNoAllocFloats - kNoAllocTail) / per) : 0;
+}
+
+int gato_solve_batched_device_noalloc(gato_plan* pl, int nsys, const float* dG_val, long long ldG, const float* dC_val,
+                                      long long ldC, const float* dg, long long ldg, const float* dc, long long ldc,
+                                      float* dlambda_out, float* ddz_out, int* diters_out, float exit_tol, int max_iters,
+                                      float rho, void* stream) {
+    int rc = check_solve_args(pl, nsys, max_iters, 0, nullptr);
+    if (rc) return rc;
+    if (!dG_val || !dC_val || !dg || !dc || !dlambda_out || !ddz_out || !diters_out)
+        return fail(GATO_EINVAL, "NULL device array");
+    if (pl->precond != 0) return fail(GATO_EUNSUPPORTED, "the no-allocation path is kernel 5: stair preconditioner only");
+    DeviceGuard guard(pl->device);
+    gato::SolveParams2 q = {};
+    gato::SolveParams& p = q.p;
+    p.gmap = pl->d_gmap; p.cmap = pl->d_cmap; p.gstart = pl->d_gstart; p.cstart = pl->d_cstart;
+    p.G_val = dG_val; p.ldG = ldG; p.C_val = dC_val; p.ldC = ldC;
+    p.g = dg; p.ldg = ldg; p.c = dc; p.ldc = ldc;
+    p.lambda_out = dlambda_out; p.ldlo = pl->n_l;
+    p.dz_out = ddz_out; p.lddz = pl->n_z;
+    p.iters_out = diters_out;
+    p.K = pl->K; p.nsys = nsys; p.max_iters = max_iters; p.warm = 0;
+    p.rho = rho; p.exit_tol = exit_tol;
+    q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
+    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
+    q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
+#define X(s, c) if (pl->S == s && pl->C == c) return launch_v5_noalloc_sc<s, c>(pl, q, (cudaStream_t)stream);
+    GATO_FOR_SIZES(X)
+#undef X
+    return fail(GATO_EUNSUPPORTED, "no kernel 5 for S=%d C=%d", pl->S, pl->C);
+}
+
+}  // extern "C"

@@ -27,6 +27,7 @@ SYMBOLS = [
     "gato_scaled_layout", "gato_scaled_debug", "gato_plan_set_scaled_chunk", "gato_plan_get_kernel_for",
     "gato_plan_set_profiling", "gato_plan_last_profile", "gato_solve_batched_multi",
     "gato_plan_set_scaled_variant", "gato_plan_set_pcg_form", "gato_plan_set_shared_matrix_path",
+    "gato_noalloc_max_systems", "gato_solve_batched_device_noalloc",
     "gato_plan_get_kernel", "gato_solve",
     "gato_solve_batched", "gato_solve_batched_device", "gato_unpack", "gato_solve_debug",
 ]
@@ -77,6 +78,9 @@ def lib():
     L.gato_plan_set_scaled_variant.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_pcg_form.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_set_shared_matrix_path.argtypes = [C.c_void_p, C.c_int]
+    L.gato_noalloc_max_systems.argtypes = [C.c_void_p]
+    L.gato_solve_batched_device_noalloc.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p, _ll] * 4 + \
+        [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_float, C.c_void_p]
     L.gato_plan_set_profiling.argtypes = [C.c_void_p, C.c_int]
     L.gato_plan_last_profile.argtypes = [C.c_void_p, _fp, _fp, _ip]
     L.gato_plan_get_kernel.argtypes = [C.c_void_p]
@@ -461,6 +465,17 @@ class Plan:
         _check(lib().gato_solve_batched_device(self._h, int(nsys), dG, ldG, dC, ldC, dg, ldg, dc, ldc,
                                                dlam_in or None, ldl, dlam_out, ddz_out, diters_out, exit_tol,
                                                int(max_iters), int(warm_start), rho, stream or None))
+
+    def noalloc_max_systems(self):
+        """Systems one `solve_batched_device_noalloc` call can take (0: kernel 5 does not hold this plan's sizes)."""
+        return int(lib().gato_noalloc_max_systems(self._h))
+
+    def solve_batched_device_noalloc(self, nsys, dG, ldG, dC, ldC, dg, ldg, dc, ldc, dlam_out, ddz_out, diters_out,
+                                     exit_tol=1e-6, max_iters=500, rho=0.0, stream=0):
+        """`gato_solve_batched_device_noalloc`: kernel 5 with its scratch in a fixed device array; the call allocates
+        nothing.  Calls that overlap on the GPU race on that array."""
+        _check(lib().gato_solve_batched_device_noalloc(self._h, int(nsys), dG, ldG, dC, ldC, dg, ldg, dc, ldc, dlam_out,
+                                                       ddz_out, diters_out, exit_tol, int(max_iters), rho, stream or None))
 
     # -- batch, any objects exposing __cuda_array_interface__ (torch, CuPy, Numba ...), zero copies --------
     def solve_batched_cuda(self, G_val, C_val, g, c, lam_out, dz_out, iters_out, lambda_in=None, exit_tol=1e-6,

@@ -224,6 +224,24 @@ int gato_plan_set_scaled_variant(gato_plan* plan, int variant);
  * system, and the second half reads the one scratch.  on = 1 (default) takes that path with the throughput second
  * half; on = 0 recomputes everything per system (the path the parity tests compare it with). */
 int gato_plan_set_shared_matrix_path(gato_plan* plan, int on);
+/* NO COUNTERPART IN THE REFERENCE.  For callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it): kernel 5 on device-resident inputs and
+ * outputs, as gato_solve_batched_device, with its scratch (unpack + Schur + congruence results handed from its first
+ * kernel to its second) in ONE file-scope `static __device__` array of GATO_NOALLOC_SCRATCH_BYTES instead of a buffer
+ * the plan grows with cudaMalloc.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine);
+ * the plan itself was allocated when it was created.  Limits: stair preconditioner, no true warm start (lambda_in is not
+ * taken), S = 14 and K <= 56 (kernel 5), and nsys <= gato_noalloc_max_systems(plan) = (8 MiB - 4 KiB) / (K * 4352 B):
+ * 38 systems at K = 50; beyond that GATO_EINVAL with the limit in gato_last_error().  Every GPU that loads the library
+ * holds the 8 MiB until exit.  ALL calls on a device share the array and it keeps the last call's contents (the call
+ * clears the one word that must start at zero, the work counter): calls that overlap on the GPU -- two streams, two
+ * plans, two host threads -- race on it; order them on one stream.  Results: the same bits as gato_solve_batched_device
+ * with kernel 5 selected (same kernels, same second-half variant rule). */
+#define GATO_NOALLOC_SCRATCH_BYTES (8ll << 20)
+int gato_noalloc_max_systems(const gato_plan* plan);   /* 0: kernel 5 does not hold this plan's sizes */
+int gato_solve_batched_device_noalloc(gato_plan* plan, int nsys, const float* dG_val, long long ldG, const float* dC_val,
+                                      long long ldC, const float* dg, long long ldg, const float* dc, long long ldc,
+                                      float* dlambda_out, float* ddz_out, int* diters_out, float exit_tol, int max_iters,
+                                      float rho, void* stream);
 /* Kernel 5, throughput second half: 0 = the update order of src/gato_pcg.cuh:348-421 (two reductions per iteration),
  * 1 = the single-reduction form of the same iteration (Chronopoulos-Gear: r~ = P^-1 r and w = S r~ first, then
  * gamma = r.r~ and delta = r~.w reduced together; s = S p by recurrence).  Same exit rule and iteration numbering;
