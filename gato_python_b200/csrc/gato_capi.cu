@@ -367,27 +367,43 @@ int launch_v5_second_lat(gato_plan* pl, const gato::SolveParams2& q, cudaStream_
     return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
 }
 
+// throughput second half with NT threads per CTA (two lanes per knot: horizons up to NT / 2 knots).  The kernel needs
+// 168 registers whatever NT is, so a shorter horizon gets more CTAs per SM instead of idle warps: 128 threads x 3 CTAs,
+// 96 x 4, 64 x 6, 32 x 12 (measured at K = 48: 1.52 ms per 8192 systems with 96 x 4 against 1.86 ms with 128 x 3).
+template <int S, int C, int NT>
+int launch_v5_second_nt(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st) {
+    using L = gato::Layout2<S, C>;
+    constexpr int NKP = NT / 2;
+    constexpr size_t smem = (size_t)(4 * (2 * (NKP + 2) * L::HALFP + 4) + NKP * (L::VS + L::LDC) + 64 + 4) * sizeof(float);
+    auto kern = pl->pcg_form == 1 ? gato::gato_pcg_scaled<S, C, NT, true> : gato::gato_pcg_scaled<S, C, NT, false>;
+    if (pl->occp_val == 0 || pl->occp_form != pl->pcg_form) {
+        int occ = 0;
+        GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+        if (occ < 1) return fail(GATO_EUNSUPPORTED, "second half of kernel 5 does not fit an SM");
+        pl->occp_val = occ;
+        pl->occp_form = pl->pcg_form;
+    }
+    const int resident = pl->occp_val * (pl->sm_count > 0 ? pl->sm_count : 148);
+    const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
+    kern<<<grid, NT, smem, st>>>(q);
+    GATO_CUDA(cudaGetLastError());
+    return GATO_OK;
+}
+
+// Horizons a few knots beyond a multiple of 16 leave the last warp nearly empty (K = 50: 4 of 32 lanes), and that warp
+// costs a full share of issue slots.  Built and measured against it: the knots beyond 48 as "tail" knots on 16 lanes
+// each (psi rows and columns from shared memory, no shuffles) as a short second pass of one warp, 96 threads and four
+// systems per SM -- 2.20 ms per 8192 systems against 1.87 ms: the tail's 16 128-bit shared-memory loads per product land
+// on the LSU pipe that is already 58 % busy, and the warp that runs them lengthens every barrier interval.  Not kept.
 template <int S, int C>
 int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st, bool lat) {
     if constexpr (HasV5<S>::value) {
-        using L = gato::Layout2<S, C>;
         if (lat) return launch_v5_second_lat<S, C>(pl, q, st);
-        constexpr int NT = kV5Threads, NKP = NT / 2;
-        constexpr size_t smem = (size_t)(4 * (2 * (NKP + 2) * L::HALFP + 4) + NKP * (L::VS + L::LDC) + 64 + 4) * sizeof(float);
-        auto kern = pl->pcg_form == 1 ? gato::gato_pcg_scaled<S, C, NT, true> : gato::gato_pcg_scaled<S, C, NT, false>;
-        if (pl->occp_val == 0 || pl->occp_form != pl->pcg_form) {
-            int occ = 0;
-            GATO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
-            if (occ < 1) return fail(GATO_EUNSUPPORTED, "second half of kernel 5 does not fit an SM");
-            pl->occp_val = occ;
-            pl->occp_form = pl->pcg_form;
-        }
-        const int resident = pl->occp_val * (pl->sm_count > 0 ? pl->sm_count : 148);
-        const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
-        kern<<<grid, NT, smem, st>>>(q);
-        GATO_CUDA(cudaGetLastError());
-        return GATO_OK;
+        if (2 * pl->K <= 32) return launch_v5_second_nt<S, C, 32>(pl, q, st);
+        if (2 * pl->K <= 64) return launch_v5_second_nt<S, C, 64>(pl, q, st);
+        if (2 * pl->K <= 96) return launch_v5_second_nt<S, C, 96>(pl, q, st);
+        return launch_v5_second_nt<S, C, kV5Threads>(pl, q, st);
     }
     return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
 }

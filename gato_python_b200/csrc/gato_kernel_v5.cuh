@@ -42,7 +42,7 @@ namespace gato {
 
 // ONE_RED: the single-reduction form of the same iteration (gato_plan_set_pcg_form).
 template <int S, int C, int NT, bool ONE_RED = false>
-__global__ void __launch_bounds__(NT, GATO_V5_CTAS) gato_pcg_scaled(const SolveParams2 q) {
+__global__ void __launch_bounds__(NT, (GATO_V5_CTAS * 128) / NT) gato_pcg_scaled(const SolveParams2 q) {
     using L = Layout2<S, C>;
     using SL = ScaledLayout<S, C>;
     constexpr int VS = L::VS, HALFP = L::HALFP, HALFU = L::HALFU, LDC = L::LDC;

@@ -321,6 +321,29 @@ def test_kernel5_solve_vs_oracle(name):
     pl.close()
 
 
+@pytest.mark.parametrize("K", [1, 9, 16, 17, 32, 33, 48, 49, 56])
+def test_kernel5_throughput_variant_at_every_cta_size(K):
+    """The throughput second half runs 32 / 64 / 96 / 128 threads per system by horizon (two lanes per knot; more systems
+    per SM for the shorter ones): each size, at its edges, against the oracle, and a batch against single solves."""
+    n = 40
+    b = iiwa_like_batch_fast(n, 14, 7, K, seed=900 + K)
+    pl = Plan(14, 7, K, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
+    pl.set_kernel(5)
+    pl.set_scaled_variant(2)
+    lam, dz, it, _ = pl.solve_batched(b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    for i in (0, 1, n // 2, n - 1):
+        prob = _sys_of(b, i)
+        lam_o, dz_o, io = oracle(prob)
+        if K == 1:
+            assert close(lam[i], lam_o) and np.abs(dz[i] - dz_o).max() < 1e-6 * np.abs(lam_o).max()
+        else:
+            assert close(lam[i], lam_o) and close(dz[i], dz_o), (i, rel2(lam[i], lam_o), rel2(dz[i], dz_o))
+        assert abs(int(it[i]) - io["iters"]) <= 1
+        l1, d1, i1 = gpu(pl, prob)
+        assert np.array_equal(l1, lam[i]) and np.array_equal(d1, dz[i]) and i1["iters"] == it[i]
+    pl.close()
+
+
 def test_kernel5_vs_reference_goldens():
     import json
     here = os.path.dirname(os.path.abspath(__file__))
