@@ -414,8 +414,6 @@ constexpr int kV5SharedChunk = 1 << 16;   // systems per gamma^ array of the sha
 template <int S, int C>
 int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool first_only) {
     if (!v5_ok_sc<S, C>(pl)) return fail(GATO_EUNSUPPORTED, "kernel 5 does not hold S=%d K=%d", pl->S, pl->K);
-    if (q.p.warm == 2)
-        return fail(GATO_EUNSUPPORTED, "kernel 5 has no true warm start yet (use kernel 2 for GATO_WARM_TRUE)");
     const long long per = v5_scratch_per_system<S, C>(pl);
     const int sms = pl->sm_count > 0 ? pl->sm_count : 148;
     // measured (profiles/r02_k5_chunk_sweep.json): larger chunks win although the scratch then leaves L2 -- the tail of
@@ -441,7 +439,8 @@ int launch_v5_sc(gato_plan* pl, gato::SolveParams2 q, cudaStream_t st, bool firs
     const bool prof = pl->profile && !first_only;
     // One matrix pair for the whole call (ldG == ldC == 0): theta, phi, M and psi are computed ONCE; a small kernel
     // forms gamma^ of every system and the second half reads the one scratch.  (Throughput variant only.)
-    const bool shared = !first_only && !lat && pl->v5_shared != 1 && base.nsys > 1 && base.ldG == 0 && base.ldC == 0;
+    // (not with a true warm start: gamma^ of that path knows nothing of lambda0)
+    const bool shared = !first_only && !lat && pl->v5_shared != 1 && base.nsys > 1 && base.ldG == 0 && base.ldC == 0 && base.warm != 2;
     const int nchunk = shared ? (base.nsys + kV5SharedChunk - 1) / kV5SharedChunk : (base.nsys + chunk - 1) / chunk;
     if (prof) {
         while ((int)pl->prof_ev.size() < 3 * nchunk) {
@@ -776,12 +775,12 @@ bool use_v5(const gato_plan* pl) { return pl->kernel == 5 && pl->precond == 0 &&
 
 // automatic choice for a call of `nsys` systems: kernel 5 for batches that fill the device (>= two systems per SM) (its two kernels keep two to
 // three systems per SM in flight: measured 2.3 M vs 2.0 M solves/s at 8192 IIWA-50 systems), the one-CTA kernel for
-// single solves and small batches (one launch; the zero-copy single solve needs its TMA staging) and for true warm
-// starts, which kernel 5 does not implement
+// single solves and small batches (one launch; the zero-copy single solve needs its TMA staging)
 bool use_v5_for(const gato_plan* pl, int nsys, int warm) {
     if (pl->precond != 0) return false;      // kernel 5 is the stair preconditioner in scaled coordinates: block-Jacobi runs on kernels 1-4
     if (pl->kernel == 5) return v5_ok(pl);
-    if (pl->kernel != 0 || pl->cl_override > 0 || warm == 2) return false;
+    (void)warm;   // (true warm start included since the first half forms r0 = gamma - S lambda0)
+    if (pl->kernel != 0 || pl->cl_override > 0) return false;
     if (pl->batch_hint > 0) nsys = pl->batch_hint;
     return nsys >= 2 * (pl->sm_count > 0 ? pl->sm_count : 148) && v5_ok(pl);   // below two waves of the one-CTA kernel it is not ahead
 }

@@ -175,7 +175,7 @@ def test_cluster_shapes_agree(cl):
     pl.close()
 
 
-@pytest.mark.parametrize("kernel", [1, 2, 3], ids=["cluster", "onecta", "onecta_cluster"])
+@pytest.mark.parametrize("kernel", [1, 2, 3, 5], ids=["cluster", "onecta", "onecta_cluster", "scaled"])
 def test_true_warm_start_extension(kernel):
     prob = CASES["iiwa50_s0"]()
     pl = plan_of(prob)
@@ -284,7 +284,7 @@ def test_full_size_batch_properties(kernel):
     c = (0.01 * rng.standard_normal((n, base["c"].size))).astype(np.float32)
     c[:, :14] = 0
     pl = plan_of(base)
-    assert pl.kernel_for(n) == 5 and pl.kernel_for(1) == 2 and pl.kernel_for(n, WARM_TRUE) == 2
+    assert pl.kernel_for(n) == 5 and pl.kernel_for(1) == 2 and pl.kernel_for(n, WARM_TRUE) == 5
     pl.set_kernel(kernel)
     if kernel == 5:
         pl.set_scaled_variant(2)      # single solves below would take the latency variant: keep the batch's kernel

@@ -344,6 +344,45 @@ def test_kernel5_throughput_variant_at_every_cta_size(K):
     pl.close()
 
 
+@pytest.mark.parametrize("variant", [1, 2], ids=["latency", "throughput"])
+def test_kernel5_true_warm_start_batch(variant):
+    """GATO_WARM_TRUE in kernel 5 (the second half iterates on the correction): a batch with per-system matrices and
+    per-system lambda0 against the oracle's true warm start and against the one-CTA kernel; lambda0 = the solution
+    converges at once; the shared-matrix form of the call takes the per-system path."""
+    n = 300
+    b = iiwa_like_batch_fast(n, 14, 7, 50, seed=321)
+    pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
+    pl.set_kernel(5)
+    pl.set_scaled_variant(variant)
+    cold = (b["G_val"], b["C_val"], b["g"], b["c"], None, b["exit_tol"], b["max_iters"], 0, b["rho"])
+    lam_c, dz_c, it_c, _ = pl.solve_batched(*cold)
+    rng = np.random.default_rng(5)
+    lam0 = (lam_c * (0.5 + 0.4 * rng.random((n, 1)))).astype(np.float32)
+    warm = (b["G_val"], b["C_val"], b["g"], b["c"], lam0, b["exit_tol"], b["max_iters"], WARM_TRUE, b["rho"])
+    lam_w, dz_w, it_w, _ = pl.solve_batched(*warm)
+    for i in range(0, n, 37):
+        lam_o, dz_o, io = oracle(_sys_of(b, i), lambda0=lam0[i], warm=True, true_warm_start=True)
+        assert close(lam_w[i], lam_o) and close(dz_w[i], dz_o), (i, rel2(lam_w[i], lam_o), rel2(dz_w[i], dz_o))
+        assert abs(int(it_w[i]) - io["iters"]) <= 1, (i, it_w[i], io["iters"])
+    p2 = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
+    p2.set_kernel(2)
+    lam_2, dz_2, it_2, _ = p2.solve_batched(*warm)
+    assert np.abs(it_2.astype(int) - it_w.astype(int)).max() <= 1
+    assert max(rel2(lam_w[i], lam_2[i]) for i in range(n)) < 1e-4 and max(rel2(dz_w[i], dz_2[i]) for i in range(n)) < 1e-4
+    p2.close()
+    # started from the solution at a looser tolerance: done within two iterations, same lambda
+    again = (b["G_val"], b["C_val"], b["g"], b["c"], lam_c, 1e-4, b["max_iters"], WARM_TRUE, b["rho"])
+    lam_a, _, it_a, _ = pl.solve_batched(*again)
+    assert it_a.max() <= 2 and max(rel2(lam_a[i], lam_c[i]) for i in range(n)) < 1e-4
+    # one matrix pair for the call + true warm start: the per-system path (the gamma^ kernel knows nothing of lambda0)
+    sh = (b["G_val"][0], b["C_val"][0], b["g"], b["c"], lam0, b["exit_tol"], b["max_iters"], WARM_TRUE, b["rho"])
+    lam_s, dz_s, it_s, _ = pl.solve_batched(*sh)
+    prob = dict(_sys_of(b, 9), G_val=b["G_val"][0], C_val=b["C_val"][0])
+    lam_o, dz_o, io = oracle(prob, lambda0=lam0[9], warm=True, true_warm_start=True)
+    assert close(lam_s[9], lam_o) and close(dz_s[9], dz_o) and abs(int(it_s[9]) - io["iters"]) <= 1
+    pl.close()
+
+
 def test_kernel5_vs_reference_goldens():
     import json
     here = os.path.dirname(os.path.abspath(__file__))
