@@ -104,7 +104,7 @@ struct gato_plan {
     // device: pattern maps
     int *d_gmap = nullptr, *d_cmap = nullptr, *d_gstart = nullptr, *d_cstart = nullptr;
     int *d_gdst2 = nullptr, *d_cdst2 = nullptr;   // v2: absolute shared-memory destinations
-    int* d_cperm = nullptr;                       // v2, one CTA: (C_val index, destination) pairs in bank-sorted order
+    int* d_cperm = nullptr;                       // v2, one CTA: (destination << kPermShift) | C_val index, in bank-sorted order
     int ncperm = 0;
     // device: staged inputs / outputs for the host-buffer entry points
     DevBuf dG, dC, dg, dc, dl, dlo, ddz, dit, dbg;
@@ -672,7 +672,7 @@ void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::
 // puts the entries of one row of [A | B] next to each other, and those sit VS = 16 words apart: 16 of 32 lanes on one
 // bank (measured 21.1 M shared-memory wavefronts per launch where 2.2 M are needed).  Greedy edge colouring of the
 // bipartite (source bank, destination bank) multigraph: each entry goes to the first warp store that has both banks
-// free; the unused lanes of a store carry destination -1.  -> interleaved (source, destination) pairs.
+// free; the unused lanes of a store carry -1.  -> one word per entry, (destination << kPermShift) | source.
 std::vector<int> v2_bank_sorted_scatter(const std::vector<int>& cdst) {
     struct Grp { unsigned src = 0, dst = 0; int n = 0; int e[32]; };
     std::vector<Grp> grp;
@@ -688,12 +688,9 @@ std::vector<int> v2_bank_sorted_scatter(const std::vector<int>& cdst) {
         while (first_open < grp.size() && grp[first_open].n == 32) ++first_open;
     }
     std::vector<int> out;
-    out.reserve(grp.size() * 64);
+    out.reserve(grp.size() * 32);
     for (const Grp& g : grp)
-        for (int i = 0; i < 32; ++i) {
-            out.push_back(i < g.n ? g.e[i] : 0);
-            out.push_back(i < g.n ? cdst[g.e[i]] : -1);
-        }
+        for (int i = 0; i < 32; ++i) out.push_back(i < g.n ? (cdst[g.e[i]] << gato::kPermShift) | g.e[i] : -1);
     return out;
 }
 
@@ -854,7 +851,7 @@ int launch_solve_v2(const gato_plan* pl, const gato::SolveParams& p, cudaStream_
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
-    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
+    q.cperm = pl->d_cperm; q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v2_sc<s, c>(pl, q, st);
     GATO_FOR_SIZES(X)
@@ -866,7 +863,7 @@ int launch_solve_v5(gato_plan* pl, const gato::SolveParams& p, cudaStream_t st, 
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
-    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
+    q.cperm = pl->d_cperm; q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v5_sc<s, c>(pl, q, st, first_only);
     GATO_FOR_SIZES(X)
@@ -878,7 +875,7 @@ int launch_solve_v2cl(const gato_plan* pl, const gato::SolveParams& p, cudaStrea
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
-    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
+    q.cperm = pl->d_cperm; q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v2cl_sc<s, c>(pl, q, st);
     GATO_FOR_SIZES(X)
@@ -898,7 +895,7 @@ int launch_solve_v2grid(gato_plan* pl, const gato::SolveParams& p, cudaStream_t 
     gato::SolveParams2 q = {};
     q.p = p;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
-    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
+    q.cperm = pl->d_cperm; q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v2grid_sc<s, c>(pl, q, st);
     GATO_FOR_SIZES(X)
@@ -1005,7 +1002,7 @@ int gato_solve_batched_device_noalloc(gato_plan* pl, int nsys, const float* dG_v
     p.K = pl->K; p.nsys = nsys; p.max_iters = max_iters; p.warm = 0;
     p.rho = rho; p.exit_tol = exit_tol;
     q.gdst = pl->d_gdst2; q.cdst = pl->d_cdst2;
-    q.cperm = reinterpret_cast<const int2*>(pl->d_cperm); q.ncperm = pl->ncperm;
+    q.cperm = pl->d_cperm; q.ncperm = pl->ncperm;
     q.nnzG = pl->nnzG; q.nnzC = pl->nnzC; q.g_diag = pl->g_diag;
 #define X(s, c) if (pl->S == s && pl->C == c) return launch_v5_noalloc_sc<s, c>(pl, q, (cudaStream_t)stream);
     GATO_FOR_SIZES(X)

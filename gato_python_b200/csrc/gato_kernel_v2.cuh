@@ -222,14 +222,16 @@ struct SolveParams2 {
     // every system into gam, and the second half reads psi / M / the regions from the one scratch (scr_ld = 0), gamma^
     // from gam and q, r from the caller's g.
     // one-CTA kernels with staged values: the non-zeros of C in an order whose every 32 consecutive entries hit 32
-    // distinct banks on both sides of the scatter -- (index into C_val, shared-memory destination) pairs, destination -1 =
-    // padding; null: scatter in CSR order through cdst
-    const int2* cperm;
+    // distinct banks on both sides of the scatter -- one word per entry, (shared-memory destination << kPermShift) | index
+    // into C_val, -1 = padding; null: scatter in CSR order through cdst
+    const int* cperm;
     int ncperm;
     float* shx;
     float* gam;           // [nsys][K VS] gamma^ in pos layout, or null: gamma^ sits in the scratch
     long long gam_ld;
 };
+
+constexpr int kPermShift = 14;   // bank-sorted scatter map: low bits = index into C_val (< 16384), high bits = destination (< 2^17)
 
 // ---- TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier) ---------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
@@ -317,8 +319,10 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // per-system scratch q.scr), together with a verbatim copy of the knot regions for the dz phase of the second half.
 // Development builds (-DGATO_S_TRACE): thread 0 of CTA 0 accumulates clock64() differences between the phase boundaries
 // of every system it takes (static shared memory) and leaves the sums 2 KB behind the work counter of kernel 5.
-// 1: fetch the first round of the bank-sorted scatter map before shared memory is cleared (measured: the 48 live
-// registers spill, 1.38 vs 1.32 ms per 8192 systems -- off)
+// 1: fetch the first round of the bank-sorted scatter map before shared memory is cleared (first half of kernel 5 only).
+// Measured three ways -- 24 (index, destination) pairs per thread: the 48 live registers spill, 1.38 vs 1.32 ms per 8192
+// systems; 22 packed words per thread, plain loads: ptxas sinks them back to their use; the same as volatile loads: no
+// spills and no gain (the scatter of C stays at ~3 750 cycles per system: it is not waiting for the map) -- off.
 #ifndef GATO_PERM_PREFETCH
 #define GATO_PERM_PREFETCH 0
 #endif
@@ -603,17 +607,23 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 
         // The scatter map of C in bank-sorted order (one-CTA kernels, staged values): its first round is fetched now and
         // arrives while shared memory is cleared.
-        constexpr int UP = 24;
+        constexpr int UP = 22;   // IIWA-50: 9 184 entries over 224 threads in two rounds of 22
         const bool permuted = !CL && staged && q.cperm != nullptr;
-        int2 pe[UP];
-        auto load_perm = [&](int t0) {
+        int pe[UP], pf[UP];      // two rounds in flight: the next one's map loads are issued before this one's scatter
+        auto load_perm = [&](int t0, int (&dst)[UP]) {
 #pragma unroll
             for (int u = 0; u < UP; ++u) {
                 const int t = t0 + u * NT;
-                pe[u] = t < q.ncperm ? __ldg(q.cperm + t) : make_int2(0, -1);
+                if constexpr (GATO_PERM_PREFETCH && SCALED) {   // volatile: ptxas otherwise sinks the loads to their use
+                    dst[u] = -1;
+                    if (t < q.ncperm) asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(dst[u]) : "l"(q.cperm + t));
+                } else {
+                    dst[u] = t < q.ncperm ? __ldg(q.cperm + t) : -1;
+                }
             }
         };
-        if (GATO_PERM_PREFETCH && permuted) load_perm(tid);
+        constexpr bool PREFETCH = GATO_PERM_PREFETCH && SCALED;   // (the full one-CTA kernel has no registers to park it in: it spills)
+        if (PREFETCH && permuted) load_perm(tid, pe);
         stamp(p, 0); S_STAMP(0);
         {   // zero everything: sparse patterns leave structural zeros, halos and pads must read as 0.
             // A persistent CTA's later systems with a purely diagonal G write exactly the words its first system
@@ -658,15 +668,21 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 // the staged copy of C_val through a pointer the compiler knows to be shared memory: a generic load of 32
                 // scattered words is split per 128-byte line before it reaches the banks (measured: 2.3 x the whole phase)
                 const float* CvS = smem + q.stage_off + stage_span(p.C_val + (long long)sys * p.ldC, q.nnzC).lead;
-#pragma unroll 1
-                for (int t0 = tid; t0 < q.ncperm; t0 += NT * UP) {
-                    if (!GATO_PERM_PREFETCH || t0 != tid) load_perm(t0);
+                auto scatter = [&](const int (&e)[UP]) {
                     float v[UP];
 #pragma unroll
-                    for (int u = 0; u < UP; ++u) v[u] = pe[u].y >= 0 ? CvS[pe[u].x] : 0.f;
+                    for (int u = 0; u < UP; ++u) v[u] = e[u] >= 0 ? CvS[e[u] & ((1 << kPermShift) - 1)] : 0.f;
 #pragma unroll
                     for (int u = 0; u < UP; ++u)
-                        if (pe[u].y >= 0) smem[pe[u].y] = v[u];
+                        if (e[u] >= 0) smem[e[u] >> kPermShift] = v[u];
+                };
+                if (!PREFETCH) load_perm(tid, pe);
+#pragma unroll 1
+                for (int t0 = tid; t0 < q.ncperm; t0 += 2 * NT * UP) {
+                    load_perm(t0 + NT * UP, pf);
+                    scatter(pe);
+                    if (t0 + 2 * NT * UP < q.ncperm) load_perm(t0 + 2 * NT * UP, pe);
+                    scatter(pf);
                 }
             } else
 #pragma unroll 1
@@ -684,6 +700,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 for (int u = 0; u < UB; ++u)
                     if (m[u] >= 0) smem[m[u] - shift] = v[u];
             }
+            S_STAMP(12);
             constexpr int UG = 8;
 #pragma unroll 1
             for (int t0 = tid; t0 < max(gB - gA, zB - zA); t0 += NT * UG) {
@@ -708,6 +725,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 }
             }
         }
+        S_STAMP(13);
         __syncthreads();
         if (!CL && staged && tid == 0 && sys + (int)gridDim.x < p.nsys) {
             // the staging area has been consumed (barrier above): fetch the next system's values now, so

@@ -18,7 +18,7 @@ st = torch.cuda.current_stream()
 names = {0: "loop head", 1: "clear shared memory + barrier", 10: "wait for the staged values (TMA)", 2: "unpack scatter + barrier",
          3: "R^-1 / Q^-1 (pass 0) + barrier", 4: "phi, BR, theta, gamma (pass 1)", 5: "region copy to global, phi -> registers, barrier",
          6: "FP64 elimination (14 pivots)", 7: "M, gamma^, stores, barrier", 8: "T = phi M^T (FP64)", 9: "psi = M T (FP64) + store",
-         11: "end-of-system barriers"}
+         11: "end-of-system barriers", 12: "(2a) scatter of C's values", 13: "(2b) scatter of G's values and g"}
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 b = iiwa_like_batch_fast(n, 14, 7, 50, seed=1000)
 pl = Plan(14, 7, 50, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
@@ -38,6 +38,6 @@ acc = tr[248:][1:]
 nsys_cta0 = (n + 147) // 148
 tot = float(acc.sum())
 print(json.dumps({"systems_taken_by_cta0": nsys_cta0, "cycles_per_system": tot / nsys_cta0,
-                  "phases_cycles_per_system": {f"{i}: {names[i]}": float(acc[i]) / nsys_cta0 for i in (0, 1, 10, 2, 3, 4, 5, 6, 7, 8, 9, 11)},
-                  "share": {f"{i}": float(acc[i]) / tot for i in (0, 1, 10, 2, 3, 4, 5, 6, 7, 8, 9, 11)}}, indent=1))
+                  "phases_cycles_per_system": {f"{i}: {names[i]}": float(acc[i]) / nsys_cta0 for i in (0, 1, 10, 12, 13, 2, 3, 4, 5, 6, 7, 8, 9, 11)},
+                  "share": {f"{i}": float(acc[i]) / tot for i in (0, 1, 10, 12, 13, 2, 3, 4, 5, 6, 7, 8, 9, 11)}}, indent=1))
 pl.close()
