@@ -396,6 +396,9 @@ int launch_v5_second_nt(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t
 // each (psi rows and columns from shared memory, no shuffles) as a short second pass of one warp, 96 threads and four
 // systems per SM -- 2.20 ms per 8192 systems against 1.87 ms: the tail's 16 128-bit shared-memory loads per product land
 // on the LSU pipe that is already 58 % busy, and the warp that runs them lengthens every barrier interval.  Not kept.
+// Second attempt, 128 threads: the fourth warp keeps its place but runs an instruction stream of its own (16 lanes per
+// knot, row and column of psi in the registers the other warps use for their rows: 28 FFMA and no shuffles per product)
+// -- correct, no spills, and 1.99 ms against 1.87 ms.  The nearly empty warp is not what the other warps wait for.
 template <int S, int C>
 int launch_v5_second(gato_plan* pl, const gato::SolveParams2& q, cudaStream_t st, bool lat) {
     if constexpr (HasV5<S>::value) {
