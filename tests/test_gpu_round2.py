@@ -383,6 +383,44 @@ def test_kernel5_true_warm_start_batch(variant):
     pl.close()
 
 
+def test_kernel5_randomised_sweep():
+    """Kernel 5 over a seeded random walk through its input space -- horizon 1 .. 56, diagonal or dense cost blocks, structural
+    or dense dynamics blocks, stiff or mild dynamics, rho 1e-4 .. 1e-1, cold / reference-warm / true warm start, either
+    second half -- five per-system-matrix systems each, against the oracle and, for the shared-matrix form of the same call,
+    against the per-system path bit for bit."""
+    from gato_python_b200.problems import iiwa_like_batch
+    rng = np.random.default_rng(20260)
+    n = 5
+    for trial in range(24):
+        K = int(rng.integers(1, 57))
+        dense_G, dense_AB = bool(rng.integers(0, 2)), bool(rng.integers(0, 2))
+        preset = ("stiff", "mild")[int(rng.integers(0, 2))]
+        rho = float(10.0 ** rng.uniform(-4, -1))
+        variant = int(rng.integers(1, 3))
+        warm = int(rng.integers(0, 3))
+        b = iiwa_like_batch(n, K=K, seed0=7000 + 10 * trial, preset=preset, dense_G=dense_G, dense_AB=dense_AB, rho=rho)
+        pl = Plan(14, 7, K, b["G_row"], b["G_col"], b["C_row"], b["C_col"], max_batch=n)
+        pl.set_kernel(5)
+        pl.set_scaled_variant(variant)
+        lam0 = (0.3 * rng.standard_normal((n, 14 * K))).astype(np.float32) if warm else None
+        tag = (trial, K, dense_G, dense_AB, preset, rho, variant, warm)
+        lam, dz, it, _ = pl.solve_batched(b["G_val"], b["C_val"], b["g"], b["c"], lam0, b["exit_tol"], b["max_iters"], warm, rho)
+        for i in range(n):
+            lam_o, dz_o, io = oracle(_sys_of(b, i), lambda0=lam0[i] if warm else np.zeros(14 * K), warm=bool(warm),
+                                     true_warm_start=(warm == WARM_TRUE))
+            if K == 1:
+                assert close(lam[i], lam_o) and np.abs(dz[i] - dz_o).max() < 1e-5 * max(np.abs(lam_o).max(), 1.0), tag
+            else:
+                assert close(lam[i], lam_o) and close(dz[i], dz_o), tag + (i, rel2(lam[i], lam_o), rel2(dz[i], dz_o))
+            assert abs(int(it[i]) - io["iters"]) <= 1, tag + (i, int(it[i]), io["iters"])
+        if warm != WARM_TRUE and variant == 2:
+            sh = pl.solve_batched(b["G_val"][2], b["C_val"][2], b["g"], b["c"], lam0, b["exit_tol"], b["max_iters"], warm, rho)
+            pl.set_shared_matrix_path(False)
+            ps = pl.solve_batched(b["G_val"][2], b["C_val"][2], b["g"], b["c"], lam0, b["exit_tol"], b["max_iters"], warm, rho)
+            assert all(np.array_equal(x, y) for x, y in zip(sh[:3], ps[:3])), tag
+        pl.close()
+
+
 def test_kernel5_vs_reference_goldens():
     import json
     here = os.path.dirname(os.path.abspath(__file__))
