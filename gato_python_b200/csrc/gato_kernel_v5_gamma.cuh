@@ -13,7 +13,7 @@
 namespace gato {
 
 template <int S, int C>
-__global__ void gato_gamma_scaled(const SolveParams2 q) {
+__global__ void __launch_bounds__(256, 2) gato_gamma_scaled(const SolveParams2 q) {
     using L = Layout2<S, C>;
     using SL = ScaledLayout<S, C>;
     using MS = MapState<S, C>;
@@ -58,12 +58,42 @@ __global__ void gato_gamma_scaled(const SolveParams2 q) {
         }
         return acc;
     };
+    const float* kg = q.scr + (long long)(active ? b : 0) * SL::KSCR;            // the ONE scratch (system 0 of the call)
+    const float* kp = q.scr + (long long)(active && b > 0 ? b - 1 : 0) * SL::KSCR;
+    const float* xk = q.shx + (long long)(active ? b : 0) * SL::KSHX;
+    // (B R^-1) rows of this lane, as the Schur phase forms them: the same for every system of the call
+    float br[OWN][C];
+#pragma unroll
+    for (int i = 0; i < OWN; ++i)
+#pragma unroll
+        for (int c = 0; c < C; ++c) br[i][c] = 0.f;
+    if (active && b > 0) {
+        if (q.g_diag) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const float ri = __ldg(kp + L::oR + c * LDC + c);
+                const float4 t = __ldg(reinterpret_cast<const float4*>(kp + L::oB + c * VS + po0));
+                const float e[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                for (int i = 0; i < OWN; ++i) br[i][c] = e[i] * ri;
+            }
+        } else {
+#pragma unroll 1
+            for (int k = 0; k < C; ++k) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(kp + L::oB + k * VS + po0));
+                const float e[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const float y = __ldg(kp + L::oR + k * LDC + c);
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i) br[i][c] = fmaf(e[i], y, br[i][c]);
+                }
+            }
+        }
+    }
     for (int sys = (int)blockIdx.x; sys < p.nsys; sys += (int)gridDim.x) {
         const float* gv = p.g + (long long)sys * p.ldg;
         const float* cv = p.c + (long long)sys * p.ldc;
-        const float* kg = q.scr + (long long)(active ? b : 0) * SL::KSCR;            // the ONE scratch (system 0 of the call)
-        const float* kp = q.scr + (long long)(active && b > 0 ? b - 1 : 0) * SL::KSCR;
-        const float* xk = q.shx + (long long)(active ? b : 0) * SL::KSHX;
         float gam[OWN];
 #pragma unroll
         for (int i = 0; i < OWN; ++i) gam[i] = 0.f;
@@ -83,44 +113,23 @@ __global__ void gato_gamma_scaled(const SolveParams2 q) {
                 for (int k = 0; k < S; ++k) qp[k] = __ldg(gv + (b - 1) * (S + C) + k);
 #pragma unroll
                 for (int k = 0; k < C; ++k) rp[k] = __ldg(gv + (b - 1) * (S + C) + S + k);
-                // (B R^-1) rows of this lane, as the Schur phase forms them
-                float br[OWN][C];
+                float a1[OWN];       // phi_b q_{b-1}, own rows: column k of phi_b holds them as one float4
 #pragma unroll
-                for (int i = 0; i < OWN; ++i)
+                for (int i = 0; i < OWN; ++i) a1[i] = 0.f;
 #pragma unroll
-                    for (int c = 0; c < C; ++c) br[i][c] = 0.f;
-                if (q.g_diag) {
-#pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        const float ri = __ldg(kp + L::oR + c * LDC + c);
-                        const float4 t = __ldg(reinterpret_cast<const float4*>(kp + L::oB + c * VS + po0));
-                        const float e[4] = {t.x, t.y, t.z, t.w};
-#pragma unroll
-                        for (int i = 0; i < OWN; ++i) br[i][c] = e[i] * ri;
-                    }
-                } else {
-#pragma unroll 1
-                    for (int k = 0; k < C; ++k) {
-                        const float4 t = __ldg(reinterpret_cast<const float4*>(kp + L::oB + k * VS + po0));
-                        const float e[4] = {t.x, t.y, t.z, t.w};
-#pragma unroll
-                        for (int c = 0; c < C; ++c) {
-                            const float y = __ldg(kp + L::oR + k * LDC + c);
-#pragma unroll
-                            for (int i = 0; i < OWN; ++i) br[i][c] = fmaf(e[i], y, br[i][c]);
-                        }
-                    }
+                for (int k = 0; k < S; ++k) {
+                    const float4 t = __ldg(reinterpret_cast<const float4*>(xk + SL::xPHI + k * VS + po0));
+                    a1[0] = fmaf(t.x, qp[k], a1[0]); a1[1] = fmaf(t.y, qp[k], a1[1]);
+                    a1[2] = fmaf(t.z, qp[k], a1[2]); a1[OWN - 1] = fmaf(t.w, qp[k], a1[OWN - 1]);
                 }
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
                     if (ovr[i]) {
                         const float a0 = qdot(kg + L::oQ + orow[i] * VS, orow[i], po0 + i, qv);
-                        float a1 = 0.f, a2 = 0.f;
-#pragma unroll
-                        for (int k = 0; k < S; ++k) a1 = fmaf(__ldg(xk + SL::xPHI + k * VS + po0 + i), qp[k], a1);
+                        float a2 = 0.f;
 #pragma unroll
                         for (int k = 0; k < C; ++k) a2 = fmaf(br[i][k], rp[k], a2);
-                        gam[i] = (a0 - __ldg(cv + b * S + orow[i])) + (a2 + a1);
+                        gam[i] = (a0 - __ldg(cv + b * S + orow[i])) + (a2 + a1[i]);
                     }
             }
         }
@@ -133,10 +142,15 @@ __global__ void gato_gamma_scaled(const SolveParams2 q) {
         for (int i = 0; i < OWN; ++i) {
             gh[i] = 0.f;
             if (active && ovr[i]) {
-                const double* mrow = reinterpret_cast<const double*>(xk + SL::xM64) + orow[i] * S;
+                const double2* mrow = reinterpret_cast<const double2*>(reinterpret_cast<const double*>(xk + SL::xM64) + orow[i] * S);
                 double acc = 0.0;
+                static_assert(S % 2 == 0 && (SL::xM64 * 4) % 16 == 0 && (SL::KSHX * 4) % 16 == 0, "rows of M64 as 16-byte loads");
 #pragma unroll
-                for (int j = 0; j < S; ++j) acc = fma(__ldg(mrow + j), (double)gfull[j], acc);   // zero above the diagonal
+                for (int j = 0; j < S; j += 2) {   // zero above the diagonal
+                    const double2 m = __ldg(mrow + j / 2);
+                    acc = fma(m.x, (double)gfull[j], acc);
+                    acc = fma(m.y, (double)gfull[j + 1], acc);
+                }
                 gh[i] = (float)acc;
             }
         }
