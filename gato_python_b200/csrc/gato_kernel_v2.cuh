@@ -323,6 +323,9 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // Measured three ways -- 24 (index, destination) pairs per thread: the 48 live registers spill, 1.38 vs 1.32 ms per 8192
 // systems; 22 packed words per thread, plain loads: ptxas sinks them back to their use; the same as volatile loads: no
 // spills and no gain (the scatter of C stays at ~3 750 cycles per system: it is not waiting for the map) -- off.
+#ifndef GATO_PERM_UP
+#define GATO_PERM_UP 22
+#endif
 #ifndef GATO_PERM_PREFETCH
 #define GATO_PERM_PREFETCH 0
 #endif
@@ -607,7 +610,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
 
         // The scatter map of C in bank-sorted order (one-CTA kernels, staged values): its first round is fetched now and
         // arrives while shared memory is cleared.
-        constexpr int UP = 22;   // IIWA-50: 9 184 entries over 224 threads in two rounds of 22
+        constexpr int UP = GATO_PERM_UP;   // IIWA-50: 9 184 entries over 224 threads in two rounds of 22
         const bool permuted = !CL && staged && q.cperm != nullptr;
         int pe[UP], pf[UP];      // two rounds in flight: the next one's map loads are issued before this one's scatter
         auto load_perm = [&](int t0, int (&dst)[UP]) {
