@@ -235,7 +235,9 @@ int gato_plan_set_shared_matrix_path(gato_plan* plan, int on);
  * holds the 8 MiB until exit.  ALL calls on a device share the array and it keeps the last call's contents (the call
  * clears the one word that must start at zero, the work counter): calls that overlap on the GPU -- two streams, two
  * plans, two host threads -- race on it; order them on one stream.  Results: the same bits as gato_solve_batched_device
- * with kernel 5 selected (same kernels, same second-half variant rule). */
+ * with kernel 5 selected (same kernels, same second-half variant rule).  Under stream capture: make one call outside the
+ * capture first (it resolves the array's device address and sets the kernels' attributes, once per device and plan);
+ * later calls enqueue a memset node and two kernel nodes and nothing else (tests/checks/noalloc_graph.py). */
 #define GATO_NOALLOC_SCRATCH_BYTES (8ll << 20)
 int gato_noalloc_max_systems(const gato_plan* plan);   /* 0: kernel 5 does not hold this plan's sizes */
 int gato_solve_batched_device_noalloc(gato_plan* plan, int nsys, const float* dG_val, long long ldG, const float* dC_val,
