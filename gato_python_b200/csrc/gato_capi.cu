@@ -675,7 +675,7 @@ void v2_fill_maps(const gato_plan* pl, const std::vector<int>& gmap, const std::
 // puts the entries of one row of [A | B] next to each other, and those sit VS = 16 words apart: 16 of 32 lanes on one
 // bank (measured 21.1 M shared-memory wavefronts per launch where 2.2 M are needed).  Greedy edge colouring of the
 // bipartite (source bank, destination bank) multigraph: each entry goes to the first warp store that has both banks
-// free; the unused lanes of a store carry -1.  -> one word per entry, (destination << kPermShift) | source.
+// free; the unused lanes of a store carry kPermPad.  -> one word per entry, (destination << kPermShift) | source.
 std::vector<int> v2_bank_sorted_scatter(const std::vector<int>& cdst) {
     struct Grp { unsigned src = 0, dst = 0; int n = 0; int e[32]; };
     std::vector<Grp> grp;
@@ -693,7 +693,7 @@ std::vector<int> v2_bank_sorted_scatter(const std::vector<int>& cdst) {
     std::vector<int> out;
     out.reserve(grp.size() * 32);
     for (const Grp& g : grp)
-        for (int i = 0; i < 32; ++i) out.push_back(i < g.n ? (cdst[g.e[i]] << gato::kPermShift) | g.e[i] : -1);
+        for (int i = 0; i < 32; ++i) out.push_back(i < g.n ? (cdst[g.e[i]] << gato::kPermShift) | g.e[i] : gato::kPermPad);
     return out;
 }
 

@@ -223,7 +223,7 @@ struct SolveParams2 {
     // from gam and q, r from the caller's g.
     // one-CTA kernels with staged values: the non-zeros of C in an order whose every 32 consecutive entries hit 32
     // distinct banks on both sides of the scatter -- one word per entry, (shared-memory destination << kPermShift) | index
-    // into C_val, -1 = padding; null: scatter in CSR order through cdst
+    // into C_val, kPermPad = padding; null: scatter in CSR order through cdst
     const int* cperm;
     int ncperm;
     float* shx;
@@ -231,6 +231,7 @@ struct SolveParams2 {
     long long gam_ld;
 };
 
+constexpr int kPermPad = (int)0x80000000;   // padding entry of that map: negative (skipped by the store), index bits zero
 constexpr int kPermShift = 14;   // bank-sorted scatter map: low bits = index into C_val (< 16384), high bits = destination (< 2^17)
 
 // ---- TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier) ---------------------
@@ -618,10 +619,10 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             for (int u = 0; u < UP; ++u) {
                 const int t = t0 + u * NT;
                 if constexpr (GATO_PERM_PREFETCH && SCALED) {   // volatile: ptxas otherwise sinks the loads to their use
-                    dst[u] = -1;
+                    dst[u] = kPermPad;
                     if (t < q.ncperm) asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(dst[u]) : "l"(q.cperm + t));
                 } else {
-                    dst[u] = t < q.ncperm ? __ldg(q.cperm + t) : -1;
+                    dst[u] = t < q.ncperm ? __ldg(q.cperm + t) : kPermPad;
                 }
             }
         };
@@ -671,13 +672,17 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 // the staged copy of C_val through a pointer the compiler knows to be shared memory: a generic load of 32
                 // scattered words is split per 128-byte line before it reaches the banks (measured: 2.3 x the whole phase)
                 const float* CvS = smem + q.stage_off + stage_span(p.C_val + (long long)sys * p.ldC, q.nnzC).lead;
+                // 32-bit shared-space addresses by hand (ld.shared / st.shared with one LEA each): through float pointers the
+                // same two accesses compiled to 19 instructions per entry (64-bit index arithmetic, selects for the padding)
+                const uint32_t src32 = smem_u32(CvS), dst32 = smem_u32(smem);
                 auto scatter = [&](const int (&e)[UP]) {
                     float v[UP];
 #pragma unroll
-                    for (int u = 0; u < UP; ++u) v[u] = e[u] >= 0 ? CvS[e[u] & ((1 << kPermShift) - 1)] : 0.f;
+                    for (int u = 0; u < UP; ++u)   // (a padding entry is kPermPad: sign bit set, index 0 -- read, never stored)
+                        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v[u]) : "r"(src32 + 4u * (uint32_t)(e[u] & ((1 << kPermShift) - 1))));
 #pragma unroll
                     for (int u = 0; u < UP; ++u)
-                        if (e[u] >= 0) smem[e[u] >> kPermShift] = v[u];
+                        if (e[u] >= 0) asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst32 + 4u * (uint32_t)(e[u] >> kPermShift)), "f"(v[u]) : "memory");
                 };
                 if (!PREFETCH) load_perm(tid, pe);
 #pragma unroll 1
@@ -721,7 +726,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 for (int u = 0; u < UG; ++u) {
                     const int t = zA + t0 + u * NT;
                     if (m[u] >= 0) smem[(m[u] & kMapMask) - shift] = v[u] + ((m[u] & kMapDiagBit) ? p.rho : 0.0f);
-                    if (t < zB) {   // g -> per-knot q (pos layout) | r
+                    if (t < zB) {   // g -> per-knot q (pos layout) | r  (a plan map of these destinations was tried: its load, on
+                                    // the store's critical path, cost more than the division: 3 355 vs 1 774 cycles for this loop)
                         const int k = t / (S + C), o = t - k * (S + C);
                         smem[k * KN - shift + (o < S ? L::oq + L::pos(o) : L::or_ + (o - S))] = w[u];
                     }
