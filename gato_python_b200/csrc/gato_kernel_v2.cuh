@@ -324,6 +324,9 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // Measured three ways -- 24 (index, destination) pairs per thread: the 48 live registers spill, 1.38 vs 1.32 ms per 8192
 // systems; 22 packed words per thread, plain loads: ptxas sinks them back to their use; the same as volatile loads: no
 // spills and no gain (the scatter of C stays at ~3 750 cycles per system: it is not waiting for the map) -- off.
+#ifndef GATO_RANK1_UNROLL
+#define GATO_RANK1_UNROLL 7   // k steps of phi A^T in flight (2: 7 730, 7: 7 350, 14: 7 200 cycles for the phase, but 14 spills)
+#endif
 #ifndef GATO_PERM_UP
 #define GATO_PERM_UP 22
 #endif
@@ -768,7 +771,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         // out[i][c] += sum_k X[row_i, k] * Y[c, k]:  X = [k][VS] with rows in pos layout (own rows are
         // one aligned load), Y = [k][VS] with its first index in pos layout (a whole column per k)
         auto rank1_S = [&](float (&out)[OWN][S], const float* X, const float* Y, int nk) {
-#pragma unroll 2
+            constexpr int UR = GATO_RANK1_UNROLL;
+#pragma unroll UR
             for (int k = 0; k < nk; ++k) {
                 float xv[OWN], yv[S];
                 load_own(X + k * VS, xv);
