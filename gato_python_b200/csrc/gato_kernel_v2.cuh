@@ -324,6 +324,9 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 // Measured three ways -- 24 (index, destination) pairs per thread: the 48 live registers spill, 1.38 vs 1.32 ms per 8192
 // systems; 22 packed words per thread, plain loads: ptxas sinks them back to their use; the same as volatile loads: no
 // spills and no gain (the scatter of C stays at ~3 750 cycles per system: it is not waiting for the map) -- off.
+#ifndef GATO_V5_INV_STEPS
+#define GATO_V5_INV_STEPS 2   // Newton steps on the reciprocal of a pivot in the FP64 elimination of kernel 5's first half (1: 2^-46, and 6 685 instead of 7 000 cycles for that phase: 0.2 % of the kernel -- not worth the margin)
+#endif
 #ifndef GATO_RANK1_UNROLL
 #define GATO_RANK1_UNROLL 7   // k steps of phi A^T in flight (2: 7 730, 7: 7 350, 14: 7 200 cycles for the phase, but 14 spills)
 #endif
