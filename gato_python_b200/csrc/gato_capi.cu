@@ -233,10 +233,17 @@ int v2_pick_nt(const gato_plan* pl) {   // smallest menu entry that holds K knot
     return 0;
 }
 
+#ifndef GATO_V5_COPY_WARP
+#define GATO_V5_COPY_WARP 0   // measured: the copy phase shrinks by 2 000 cycles per system and the other phases grow by as much (off)
+#endif
 template <int S, int C, int NT, bool SCALED = false>
 int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     using L = gato::Layout2<S, C>;
-    auto kern = gato::gato_fused_solve_v2<S, C, NT, false, false, SCALED>;
+    // first half of kernel 5 at the largest CTA shape: one warp more than the layout's NT threads, for the region copy
+    // (256 threads x 255 registers fill the register file exactly; the smaller shapes run several CTAs per SM instead)
+    constexpr bool XW = SCALED && NT == 224 && GATO_V5_COPY_WARP;
+    constexpr int NTT = XW ? NT + 32 : NT;
+    auto kern = gato::gato_fused_solve_v2<S, C, NT, false, false, SCALED, XW>;
     int& occ_smem = SCALED ? pl->occ5_smem : pl->occ_smem;
     int& occ_val = SCALED ? pl->occ5_val : pl->occ_val;
     const int core = L::smem_floats(q.p.K, NT);
@@ -268,14 +275,14 @@ int launch_v2_t(const gato_plan* pl, gato::SolveParams2 q, cudaStream_t st) {
     }
     if (occ_smem != (int)smem) {
         int occ = 0;
-        GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+        GATO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NTT, smem));
         if (occ < 1) return fail(GATO_EUNSUPPORTED, "one-CTA kernel does not fit an SM (%zu B shared memory)", smem);
         occ_smem = (int)smem;
         occ_val = occ;
     }
     const int resident = occ_val * (pl->sm_count > 0 ? pl->sm_count : 148);
     const unsigned grid = (unsigned)(q.p.nsys < resident ? q.p.nsys : resident);
-    kern<<<grid, NT, smem, st>>>(q);
+    kern<<<grid, NTT, smem, st>>>(q);
     GATO_CUDA(cudaGetLastError());
     return GATO_OK;
 }

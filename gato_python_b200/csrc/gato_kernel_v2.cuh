@@ -342,8 +342,11 @@ __host__ __device__ constexpr int stage_len(int n) { return (n + 8) & ~3; }   //
 #define S_STAMP(i) do { } while (0)
 #endif
 
-template <int S, int C, int NT, bool CL = false, bool GRID = false, bool SCALED = false>
-__global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 q) {
+// XW (first half of kernel 5 only): one warp MORE than the layout's NT threads.  Its lanes own no knot; while the other
+// warps form theta and eliminate, it copies the knot regions to the scratch -- a job bound by the SM's store path, which
+// costs the warp that does it ~3 400 cycles per system whatever else that warp could be doing (gato_kernel_v5_schur.inc).
+template <int S, int C, int NT, bool CL = false, bool GRID = false, bool SCALED = false, bool XW = false>
+__global__ void __launch_bounds__(XW ? NT + 32 : NT, 1) gato_fused_solve_v2(const SolveParams2 q) {
     static_assert(!GRID || CL, "the grid variant uses the cluster variant's decomposition");
     static_assert(!SCALED || !CL, "the scaled-system variant is a one-CTA kernel");
     using L = Layout2<S, C>;
@@ -353,6 +356,8 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                   HALFP = L::HALFP, HALFU = L::HALFU, KN = L::KN, LDC = L::LDC;
     constexpr bool VEC = L::VEC_OWN;
     constexpr int NW = NT / 32, NKP = NW * L::KPW, NW4 = (NW + 3) / 4;
+    constexpr int NTT = XW ? NT + 32 : NT;    // threads launched (loop strides); NT stays the layout's thread count
+    static_assert(!XW || (SCALED && !CL), "the extra warp belongs to the first half of kernel 5");
     extern __shared__ __align__(16) float smem[];
     const SolveParams& p = q.p;
     const int K = p.K;
@@ -623,7 +628,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         auto load_perm = [&](int t0, int (&dst)[UP]) {
 #pragma unroll
             for (int u = 0; u < UP; ++u) {
-                const int t = t0 + u * NT;
+                const int t = t0 + u * NTT;
                 if constexpr (GATO_PERM_PREFETCH && SCALED) {   // volatile: ptxas otherwise sinks the loads to their use
                     dst[u] = kPermPad;
                     if (t < q.ncperm) asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(dst[u]) : "l"(q.cperm + t));
@@ -640,7 +645,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             // wrote in the knot regions (same pattern, reciprocals in place): only the iterates need clearing.
             const bool keep_regions = !CL && !SCALED && q.g_diag && sys >= (int)gridDim.x;   // (kernel 5 reuses the regions as FP64 scratch)
             float4* s4 = reinterpret_cast<float4*>(smem);
-            for (int i = (keep_regions ? nreg * KN / 4 : 0) + tid; i < nfloats / 4; i += NT)
+            for (int i = (keep_regions ? nreg * KN / 4 : 0) + tid; i < nfloats / 4; i += NTT)
                 s4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         sync_all();   // cluster variant: no CTA pushes into a halo slot that its owner has yet to clear
@@ -692,20 +697,20 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 };
                 if (!PREFETCH) load_perm(tid, pe);
 #pragma unroll 1
-                for (int t0 = tid; t0 < q.ncperm; t0 += 2 * NT * UP) {
-                    load_perm(t0 + NT * UP, pf);
+                for (int t0 = tid; t0 < q.ncperm; t0 += 2 * NTT * UP) {
+                    load_perm(t0 + NTT * UP, pf);
                     scatter(pe);
-                    if (t0 + 2 * NT * UP < q.ncperm) load_perm(t0 + 2 * NT * UP, pe);
+                    if (t0 + 2 * NTT * UP < q.ncperm) load_perm(t0 + 2 * NTT * UP, pe);
                     scatter(pf);
                 }
             } else
 #pragma unroll 1
-            for (int t0 = cA + tid; t0 < cB; t0 += NT * UB) {
+            for (int t0 = cA + tid; t0 < cB; t0 += NTT * UB) {
                 int m[UB];
                 float v[UB];
 #pragma unroll
                 for (int u = 0; u < UB; ++u) {
-                    const int t = t0 + u * NT;
+                    const int t = t0 + u * NTT;
                     m[u] = -1;
                     v[u] = 0.f;
                     if (t < cB) { m[u] = __ldg(q.cdst + t); v[u] = Cv[t]; }
@@ -717,12 +722,12 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
             S_STAMP(12);
             constexpr int UG = 8;
 #pragma unroll 1
-            for (int t0 = tid; t0 < max(gB - gA, zB - zA); t0 += NT * UG) {
+            for (int t0 = tid; t0 < max(gB - gA, zB - zA); t0 += NTT * UG) {
                 int m[UG];
                 float v[UG], w[UG];
 #pragma unroll
                 for (int u = 0; u < UG; ++u) {
-                    const int t = t0 + u * NT;
+                    const int t = t0 + u * NTT;
                     m[u] = -1;
                     v[u] = w[u] = 0.f;
                     if (gA + t < gB) { m[u] = __ldg(q.gdst + gA + t); v[u] = Gv[gA + t]; }
@@ -730,7 +735,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
                 }
 #pragma unroll
                 for (int u = 0; u < UG; ++u) {
-                    const int t = zA + t0 + u * NT;
+                    const int t = zA + t0 + u * NTT;
                     if (m[u] >= 0) smem[(m[u] & kMapMask) - shift] = v[u] + ((m[u] & kMapDiagBit) ? p.rho : 0.0f);
                     if (t < zB) {   // g -> per-knot q (pos layout) | r  (a plan map of these destinations was tried: its load, on
                                     // the store's critical path, cost more than the division: 3 355 vs 1 774 cycles for this loop)
@@ -816,6 +821,26 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         }
 #pragma unroll 1
         for (int pass = 0; pass < 2; ++pass) {
+            if constexpr (XW) {
+                if (pass == 1 && warp == NW) {   // the extra warp: every knot's A | B | Q^-1 | R^-1 | q | r is final (pass 0 inverted Q and R)
+                    using SLX = ScaledLayout<S, C>;
+                    constexpr int W4 = SLX::REG / 4, Q0 = L::oQ / 4, Q1 = L::oR / 4;
+                    float* scrx = q.scr + (long long)sys * q.scr_ld;
+                    const bool skipQ = q.g_diag != 0;
+#pragma unroll 2
+                    for (int k = 0; k < K; ++k) {
+                        const float4* src = reinterpret_cast<const float4*>(smem + k * KN);
+                        float4* dst = reinterpret_cast<float4*>(scrx + (long long)k * SLX::KSCR);
+#pragma unroll
+                        for (int o0 = 0; o0 < W4; o0 += 32) {
+                            const int o = o0 + lane;
+                            if (o < W4 && !(skipQ && o >= Q0 && o < Q1)) dst[o] = src[o];
+                        }
+                        if (skipQ && lane < S)     // of a diagonal Q^-1 only the diagonal
+                            scrx[(long long)k * SLX::KSCR + L::oQ + lane * VS + L::pos(lane)] = smem[k * KN + L::oQ + lane * VS + L::pos(lane)];
+                    }
+                }
+            }
             // lanes with nothing to invert in this pass carry an identity through the warp-wide elimination
             const bool inv = pass == 0 ? (active || lhalo) : active;
 #pragma unroll
@@ -998,6 +1023,7 @@ __global__ void __launch_bounds__(NT, 1) gato_fused_solve_v2(const SolveParams2 
         __syncthreads();   // phi_b of every block row is in shared memory
 
         if constexpr (SCALED) {
+            constexpr bool kXW = XW;
 #include "gato_kernel_v5_schur.inc"
         } else {
         // ==== 4. iteration matrices into registers, matrix mapping ====================================
