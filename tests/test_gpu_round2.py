@@ -528,6 +528,32 @@ def test_kernel5_shared_matrix_path(name, K):
     pl.close()
 
 
+def test_kernel5_shared_matrix_path_beyond_one_gamma_array():
+    """More systems than one gamma^ array of the shared-matrix path holds (65 536): its second and later chunks reset the
+    work counter themselves.  Short horizon, 70 000 right-hand sides, against the per-system path bit for bit."""
+    n, K = 70000, 3
+    prob = iiwa_like(K=K, seed=21)
+    rng = np.random.default_rng(22)
+    g = (prob["g"][None, :] * (1.0 + 0.5 * rng.standard_normal((n, prob["g"].size)))).astype(np.float32)
+    c = (prob["c"][None, :] + 0.1 * rng.standard_normal((n, prob["c"].size))).astype(np.float32)
+    pl = Plan(14, 7, K, prob["G_row"], prob["G_col"], prob["C_row"], prob["C_col"], max_batch=n)
+    pl.set_kernel(5)
+    pl.set_scaled_variant(2)
+    pl.set_pipeline(-1)                 # one launch sequence for the whole batch (the host pipeline would cut it into chunks)
+    args = (prob["G_val"], prob["C_val"], g, c, None, prob["exit_tol"], prob["max_iters"], 0, prob["rho"])
+    pl.set_profiling(True)
+    lam, dz, it, _ = pl.solve_batched(*args)
+    assert pl.last_profile()[2] == 1 + 2 * 2          # first half once, then (gamma kernel, second half) per gamma^ array
+    pl.set_profiling(False)
+    pl.set_shared_matrix_path(False)
+    lam2, dz2, it2, _ = pl.solve_batched(*args)
+    assert np.array_equal(it, it2) and np.array_equal(lam, lam2) and np.array_equal(dz, dz2)
+    for i in (0, 65535, 65536, n - 1):
+        lam_o, dz_o, io = oracle(dict(prob, g=g[i], c=c[i]))
+        assert close(lam[i], lam_o) and close(dz[i], dz_o) and abs(int(it[i]) - io["iters"]) <= 1, i
+    pl.close()
+
+
 # ---- boundary hardening -------------------------------------------------------------------------------------------
 def test_multiplan_single_process_gather_vs_oracle():
     """gato_solve_batched_multi: one process, one host thread per device, results gathered into one host buffer.  With a
